@@ -1,0 +1,149 @@
+/*
+ * b2c.h -- C ABI of the B200 batched controller engine (libb2c.so).
+ *
+ * Drop-in boundary for the data-parallel hot path of the reference
+ * (citations: /root/reference/src/hybrid_controller/hybrid_controller/ = HC/):
+ *   b2c_linearize*   <- Linearizer.get_jacobians / discretize_euler / discretize_exact /
+ *                       get_discrete_model / get_discrete_model_explicit
+ *                       (HC/models/linearization.py:62-225)
+ *   b2c_dare*        <- LQRController.compute_gain / get_lqr_gain
+ *                       (HC/controllers/lqr_controller.py:92-147, :217-242)
+ *   b2c_lqr_control* <- LQRController.compute_control (+ _normalize_angle, _clip_control)
+ *                       (HC/controllers/lqr_controller.py:149-189, :244-257)
+ *   b2c_mpc*         <- MPCController.solve_with_ltv (HC/controllers/mpc_controller.py:345-522),
+ *                       MPCController.solve (:150-314), _get_fallback_solution (:316-343)
+ *
+ * Conventions
+ *   - all arithmetic and all real buffers are IEEE fp64 (the reference is numpy fp64);
+ *   - "_dev" entry points take DEVICE pointers in instance-minor SoA layout
+ *     (element [f][i] at  f*B + i ; i = instance, coalesced across a warp);
+ *   - "_host" entry points take HOST pointers in the natural instance-major layout a numpy
+ *     user holds ((B,3,3), (B,N+1,3) ...): the library stages them through pinned memory,
+ *     copies, re-lays them out on the device, runs the same kernels and copies results back;
+ *   - caller allocates every in/out buffer; the library owns only the opaque context
+ *     (stream, scratch, pinned staging);
+ *   - return value: 0 = ok, <0 = error (b2c_last_error() gives the text). Per-instance solver
+ *     outcomes are reported in status[] and never as an error code;
+ *   - a context is not thread-safe: one per host thread / per GPU.
+ *   - there is NO CPU fallback: without a CUDA device b2c_create fails.
+ */
+#ifndef B2C_H
+#define B2C_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2c_ctx b2c_ctx;
+
+/* linearization method ids (Linearizer.get_discrete_model 'method', linearization.py:160-188) */
+enum { B2C_LIN_JACOBIAN = 0,  /* continuous (A,B)            :62-96   */
+       B2C_LIN_EULER    = 1,  /* I + A dt, B dt              :98-118 (== explicit :190-225) */
+       B2C_LIN_EXACT    = 2   /* expm ZOH, closed form (A^2=0) :120-158 */ };
+
+/* low-speed guard applied to v before linearizing */
+enum { B2C_GUARD_NONE = 0,    /* get_lqr_gain                lqr_controller.py:217-242 */
+       B2C_GUARD_LQR  = 1,    /* |v|<1e-6 -> 0.01            lqr_controller.py:120-122 */
+       B2C_GUARD_MPC  = 2     /* |v|<=0.01 -> 0.1            mpc_controller.py:186,425 */ };
+
+/* per-instance status of the iterative kernels */
+enum { B2C_OK = 0, B2C_MAXITER = 1, B2C_NONFINITE = 2, B2C_INFEASIBLE = 3 };
+
+/* MPC problem kinds */
+enum { B2C_MPC_LTV = 0,       /* solve_with_ltv: error state, LTV, move blocking, theta unwrap */
+       B2C_MPC_LTI = 1        /* solve: absolute state, one linearization, no unwrap           */ };
+
+typedef struct {
+    int32_t kind;             /* B2C_MPC_LTV | B2C_MPC_LTI                                     */
+    int32_t N;                /* horizon                      (mpc_controller.py:111)           */
+    int32_t M;                /* obstacles per instance (0 allowed)                             */
+    int32_t block_size;       /* move blocking, LTV only      (:118-121)                        */
+    int32_t soft;             /* use_soft_constraints         (:152, :347)                      */
+    int32_t max_iter;         /* Newton iteration cap (<=0: default 60)                         */
+    int32_t ramp_up_steps;    /* cold-start ramp length       (:144), LTV only                  */
+    int32_t reserved;
+    double  Qd[3], Rd[2], Pd[3];
+    double  d_safe, rho, v_max, w_max, dt;
+    double  tol;              /* relative Newton-decrement tolerance (<=0: default 1e-14)       */
+} b2c_mpc_params;
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+int         b2c_create(b2c_ctx** out, int device);           /* device<0: current device       */
+int         b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream);
+void        b2c_destroy(b2c_ctx* ctx);
+const char* b2c_last_error(void);
+int         b2c_version(void);
+int         b2c_sync(b2c_ctx* ctx);                           /* cudaStreamSynchronize          */
+void*       b2c_stream(b2c_ctx* ctx);                         /* the cudaStream_t in use        */
+/* total kernel launches issued through this context since creation */
+int64_t     b2c_launch_count(b2c_ctx* ctx);
+
+/* pinned host memory for the *_host entry points (full PCIe rate; pageable memory also works) */
+int         b2c_host_alloc(void** out, int64_t bytes);
+int         b2c_host_free(void* p);
+
+/* ---- K1: Jacobian + discretization ----------------------------------------------------- */
+/* dev: v[B], th[B] -> Ad[9][B], Bd[6][B] (row-major 3x3 / 3x2 element index as field)        */
+int b2c_linearize_dev(b2c_ctx*, int64_t B, int method, int guard, double dt,
+                      const double* v, const double* th, double* Ad, double* Bd);
+/* dev, packed: the same result in numpy layout Ad (B,3,3), Bd (B,3,2)                        */
+int b2c_linearize_packed_dev(b2c_ctx*, int64_t B, int method, int guard, double dt,
+                             const double* v, const double* th, double* Ad, double* Bd);
+int b2c_linearize_host(b2c_ctx*, int64_t B, int method, int guard, double dt,
+                       const double* v, const double* th, double* Ad /*(B,3,3)*/,
+                       double* Bd /*(B,3,2)*/);
+
+/* ---- K2: DARE + LQR gain ---------------------------------------------------------------- */
+/* dev: v[B], th[B] -> K[6][B] (row-major 2x3), P[6][B] upper triangle (xx,xy,xt,yy,yt,tt) or
+ * NULL, iters[B] or NULL, status[B] or NULL.  method/guard as above (the reference uses
+ * EULER + GUARD_LQR in compute_gain, EULER + GUARD_NONE in get_lqr_gain).                    */
+int b2c_dare_dev(b2c_ctx*, int64_t B, int method, int guard, double dt,
+                 const double Qd[3], const double Rd[2],
+                 const double* v, const double* th,
+                 double* K, double* P, int32_t* iters, int32_t* status);
+/* host: K (B,2,3), P (B,3,3) full symmetric or NULL                                          */
+int b2c_dare_host(b2c_ctx*, int64_t B, int method, int guard, double dt,
+                  const double Qd[3], const double Rd[2],
+                  const double* v, const double* th,
+                  double* K, double* P, int32_t* iters, int32_t* status);
+
+/* ---- LQR control law --------------------------------------------------------------------- */
+/* dev: x[3][B], xref[3][B], uref[2][B], K[6][B] -> u[2][B], err[3][B] (wrapped) or NULL       */
+int b2c_lqr_control_dev(b2c_ctx*, int64_t B, double v_max, double w_max,
+                        const double* x, const double* xref, const double* uref,
+                        const double* K, double* u, double* err);
+
+/* ---- K3: MPC QP ---------------------------------------------------------------------------- */
+/* bytes of device scratch b2c_mpc_dev needs for (B, params); the context grows its own scratch
+ * on demand, this is informational (memory planning for 180 GB HBM).                          */
+int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B);
+
+/* dev (SoA): x0[3][B], xref[(N+1)*3][B] (field = k*3+c), uref[N*2][B], obs[M*3][B]
+ * (field = m*3+{x,y,r}), step_count[B] (in: successful solves so far; out: +1 on success; may be
+ * NULL = ramp off).  Outputs: u0[2][B], cost[B], status[B], iters[B], slack_used[B];
+ * useq[N*2][B] / xpred[(N+1)*3][B] optional (NULL to skip).
+ * For kind=LTI xref/uref must already hold N+1 / N rows (the host mirror pads, :172-183).    */
+int b2c_mpc_dev(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                const double* x0, const double* xref, const double* uref, const double* obs,
+                int32_t* step_count,
+                double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                double* useq, double* xpred);
+/* host (instance-major): x0 (B,3), xref (B,N+1,3), uref (B,N,2), obs (B,M,3), step_count (B);
+ * outputs u0 (B,2), cost (B), status/iters/slack_used (B), useq (B,N,2), xpred (B,N+1,3).    */
+int b2c_mpc_host(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                 const double* x0, const double* xref, const double* uref, const double* obs,
+                 int32_t* step_count,
+                 double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                 double* useq, double* xpred);
+
+/* ---- measurement helpers -------------------------------------------------------------------- */
+/* register-resident FMA microbenchmark: returns achieved TFLOP/s (2 flop per FMA) for fp64
+ * (bits=64) or fp32 (bits=32); used for the FP64 roofline denominator MEASURED_PEAKS lacks.   */
+int b2c_measure_fma_peak(b2c_ctx*, int bits, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2C_H */

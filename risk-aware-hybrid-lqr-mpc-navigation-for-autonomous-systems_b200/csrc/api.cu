@@ -1,0 +1,316 @@
+// Context lifecycle, host-buffer entry points (pinned staging + on-device re-layout) and the
+// FMA-peak microbenchmark of libb2c.so.
+#include <string.h>
+#include <mutex>
+#include "b2c_common.cuh"
+
+static thread_local std::string g_err;
+void b2c_set_error(const std::string& s) { g_err = s; }
+const char* b2c_last_error(void) { return g_err.c_str(); }
+int b2c_version(void) { return 100; }
+
+int b2c_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    g_err = buf;
+    return -100 - (int)e;
+}
+
+int b2c_reserve(void** p, size_t* cur, size_t need, bool pinned_host) {
+    if (need <= *cur) return 0;
+    size_t want = need + need / 4 + 4096;
+    if (*p) {
+        cudaError_t e = pinned_host ? cudaFreeHost(*p) : cudaFree(*p);
+        *p = nullptr; *cur = 0;
+        if (e != cudaSuccess) return b2c_cuda_fail(e, "free", __FILE__, __LINE__);
+    }
+    cudaError_t e = pinned_host ? cudaMallocHost(p, want) : cudaMalloc(p, want);
+    if (e != cudaSuccess) { *p = nullptr; return b2c_cuda_fail(e, "alloc", __FILE__, __LINE__); }
+    *cur = want;
+    return 0;
+}
+
+int b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream) {
+    if (!out) { b2c_set_error("null out pointer"); return -1; }
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        b2c_set_error(std::string("no CUDA device available (libb2c has no CPU fallback): ") +
+                      cudaGetErrorString(e));
+        return -10;
+    }
+    if (device < 0) B2C_CUDA(cudaGetDevice(&device));
+    B2C_CUDA(cudaSetDevice(device));
+    b2c_ctx* c = new b2c_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    B2C_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
+    else {
+        e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete c; return b2c_cuda_fail(e, "stream create", __FILE__, __LINE__); }
+        c->own_stream = true;
+    }
+    *out = c;
+    return 0;
+}
+
+int b2c_create(b2c_ctx** out, int device) { return b2c_create_on_stream(out, device, nullptr); }
+
+void b2c_destroy(b2c_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->scratch) cudaFree(c->scratch);
+    if (c->dstage) cudaFree(c->dstage);
+    if (c->hstage) cudaFreeHost(c->hstage);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int b2c_sync(b2c_ctx* c) {
+    if (!c) { b2c_set_error("null context"); return -1; }
+    B2C_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+void* b2c_stream(b2c_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int64_t b2c_launch_count(b2c_ctx* c) { return c ? c->launches : 0; }
+
+// ---- re-layout kernels: instance-major (B,F) <-> instance-minor [F][B] ----------------------
+// 32x32 tiles through shared memory so both sides are coalesced.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_aos_to_soa(int64_t B, int F, const T* __restrict__ aos, T* __restrict__ soa) {
+    __shared__ T tile[32][33];
+    const int64_t i0 = (int64_t)blockIdx.x * 32;
+    const int f0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += 8) {          // r: instance within tile
+        int64_t i = i0 + r; int f = f0 + threadIdx.x;
+        if (i < B && f < F) tile[r][threadIdx.x] = aos[i * F + f];
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += 8) {          // r: field within tile
+        int f = f0 + r; int64_t i = i0 + threadIdx.x;
+        if (i < B && f < F) soa[(int64_t)f * B + i] = tile[threadIdx.x][r];
+    }
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_soa_to_aos(int64_t B, int F, const T* __restrict__ soa, T* __restrict__ aos) {
+    __shared__ T tile[32][33];
+    const int64_t i0 = (int64_t)blockIdx.x * 32;
+    const int f0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += 8) {          // r: field
+        int f = f0 + r; int64_t i = i0 + threadIdx.x;
+        if (i < B && f < F) tile[r][threadIdx.x] = soa[(int64_t)f * B + i];
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += 8) {          // r: instance
+        int64_t i = i0 + r; int f = f0 + threadIdx.x;
+        if (i < B && f < F) aos[i * F + f] = tile[threadIdx.x][r];
+    }
+}
+// symmetric 3x3 from upper-triangle SoA [6][B] -> (B,3,3)
+__global__ void __launch_bounds__(256)
+k_sym6_to_full(int64_t B, const double* __restrict__ p6, double* __restrict__ full) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B) return;
+    double xx = p6[i], xy = p6[B + i], xt = p6[2 * B + i], yy = p6[3 * B + i], yt = p6[4 * B + i], tt = p6[5 * B + i];
+    double* o = full + i * 9;
+    o[0] = xx; o[1] = xy; o[2] = xt; o[3] = xy; o[4] = yy; o[5] = yt; o[6] = xt; o[7] = yt; o[8] = tt;
+}
+
+static int to_soa(b2c_ctx* c, int64_t B, int F, const double* aos, double* soa) {
+    if (F <= 0) return 0;
+    dim3 g((unsigned)((B + 31) / 32), (unsigned)((F + 31) / 32)), t(32, 8);
+    k_aos_to_soa<double><<<g, t, 0, c->stream>>>(B, F, aos, soa);
+    B2C_CHECK_LAUNCH(c);
+    return 0;
+}
+static int to_aos(b2c_ctx* c, int64_t B, int F, const double* soa, double* aos) {
+    if (F <= 0) return 0;
+    dim3 g((unsigned)((B + 31) / 32), (unsigned)((F + 31) / 32)), t(32, 8);
+    k_soa_to_aos<double><<<g, t, 0, c->stream>>>(B, F, soa, aos);
+    B2C_CHECK_LAUNCH(c);
+    return 0;
+}
+
+// ---- host-buffer entry points ---------------------------------------------------------------
+// cudaMemcpyAsync straight from/to the caller's buffers: pass pinned memory (b2c_host_alloc or
+// torch pin_memory) for full PCIe rate; pageable memory works but is staged by the driver.
+struct Bump {
+    char* base; size_t off = 0;
+    explicit Bump(void* b) : base((char*)b) {}
+    template <typename T> T* take(size_t n) {
+        T* p = (T*)(base + off);
+        off += ((n * sizeof(T) + 255) / 256) * 256;
+        return p;
+    }
+};
+static size_t pad256(size_t bytes) { return ((bytes + 255) / 256) * 256; }
+
+int b2c_host_alloc(void** p, int64_t bytes) {
+    if (!p || bytes < 0) { b2c_set_error("bad host alloc request"); return -1; }
+    B2C_CUDA(cudaMallocHost(p, (size_t)bytes));
+    return 0;
+}
+int b2c_host_free(void* p) {
+    if (p) B2C_CUDA(cudaFreeHost(p));
+    return 0;
+}
+
+int b2c_linearize_host(b2c_ctx* c, int64_t B, int method, int guard, double dt,
+                       const double* v, const double* th, double* Ad, double* Bd) {
+    if (!c) { b2c_set_error("null context"); return -1; }
+    if (method < 0 || method > 2) { b2c_set_error("Unknown discretization method"); return -2; }
+    if (B <= 0) return 0;
+    B2C_CUDA(cudaSetDevice(c->device));
+    size_t need = 2 * pad256(B * 8) + pad256(B * 72) + pad256(B * 48);
+    int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
+    if (rc) return rc;
+    Bump bp(c->dstage);
+    double* dv = bp.take<double>(B); double* dth = bp.take<double>(B);
+    double* dA = bp.take<double>(9 * B); double* dB = bp.take<double>(6 * B);
+    B2C_CUDA(cudaMemcpyAsync(dv, v, B * 8, cudaMemcpyHostToDevice, c->stream));
+    B2C_CUDA(cudaMemcpyAsync(dth, th, B * 8, cudaMemcpyHostToDevice, c->stream));
+    rc = b2c_linearize_packed_dev(c, B, method, guard, dt, dv, dth, dA, dB);
+    if (rc) return rc;
+    B2C_CUDA(cudaMemcpyAsync(Ad, dA, B * 72, cudaMemcpyDeviceToHost, c->stream));
+    B2C_CUDA(cudaMemcpyAsync(Bd, dB, B * 48, cudaMemcpyDeviceToHost, c->stream));
+    B2C_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int b2c_dare_host(b2c_ctx* c, int64_t B, int method, int guard, double dt,
+                  const double Qd[3], const double Rd[2], const double* v, const double* th,
+                  double* K, double* P, int32_t* iters, int32_t* status) {
+    if (!c) { b2c_set_error("null context"); return -1; }
+    if (B <= 0) return 0;
+    B2C_CUDA(cudaSetDevice(c->device));
+    size_t need = 2 * pad256(B * 8) + 2 * pad256(B * 48) + pad256(B * 48) + pad256(B * 72) + 2 * pad256(B * 4);
+    int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
+    if (rc) return rc;
+    Bump bp(c->dstage);
+    double* dv = bp.take<double>(B); double* dth = bp.take<double>(B);
+    double* dKs = bp.take<double>(6 * B); double* dKa = bp.take<double>(6 * B);
+    double* dP6 = bp.take<double>(6 * B); double* dPf = bp.take<double>(9 * B);
+    int32_t* dit = bp.take<int32_t>(B); int32_t* dst = bp.take<int32_t>(B);
+    B2C_CUDA(cudaMemcpyAsync(dv, v, B * 8, cudaMemcpyHostToDevice, c->stream));
+    B2C_CUDA(cudaMemcpyAsync(dth, th, B * 8, cudaMemcpyHostToDevice, c->stream));
+    rc = b2c_dare_dev(c, B, method, guard, dt, Qd, Rd, dv, dth, dKs, P ? dP6 : nullptr, dit, dst);
+    if (rc) return rc;
+    rc = to_aos(c, B, 6, dKs, dKa);
+    if (rc) return rc;
+    B2C_CUDA(cudaMemcpyAsync(K, dKa, B * 48, cudaMemcpyDeviceToHost, c->stream));
+    if (P) {
+        k_sym6_to_full<<<b2c_blocks(B, 256), 256, 0, c->stream>>>(B, dP6, dPf);
+        B2C_CHECK_LAUNCH(c);
+        B2C_CUDA(cudaMemcpyAsync(P, dPf, B * 72, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (iters) B2C_CUDA(cudaMemcpyAsync(iters, dit, B * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (status) B2C_CUDA(cudaMemcpyAsync(status, dst, B * 4, cudaMemcpyDeviceToHost, c->stream));
+    B2C_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int b2c_mpc_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
+                 const double* x0, const double* xref, const double* uref, const double* obs,
+                 int32_t* step_count,
+                 double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                 double* useq, double* xpred) {
+    if (!c || !p) { b2c_set_error("null context/params"); return -1; }
+    if (B <= 0) return 0;
+    if (p->N < 1 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
+    B2C_CUDA(cudaSetDevice(c->device));
+    const int N = p->N, M = p->M;
+    const int FX = 3 * (N + 1), FU = 2 * N, FO = 3 * M;
+    const size_t nin = (size_t)B * (3 + FX + FU + FO);
+    const size_t nout = (size_t)B * (2 + 1 + (useq ? FU : 0) + (xpred ? FX : 0));
+    size_t need = 2 * pad256(nin * 8) + 2 * pad256(nout * 8) + 16 * 256 + 4 * pad256(B * 4) + 8 * 256 * 4;
+    int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
+    if (rc) return rc;
+    Bump bp(c->dstage);
+    double* a_x0 = bp.take<double>(3 * B);   double* s_x0 = bp.take<double>(3 * B);
+    double* a_xr = bp.take<double>(FX * B);  double* s_xr = bp.take<double>(FX * B);
+    double* a_ur = bp.take<double>(FU * B);  double* s_ur = bp.take<double>(FU * B);
+    double* a_ob = bp.take<double>(FO * B + 1); double* s_ob = bp.take<double>(FO * B + 1);
+    double* s_u0 = bp.take<double>(2 * B);   double* a_u0 = bp.take<double>(2 * B);
+    double* d_cost = bp.take<double>(B);
+    double* s_us = useq ? bp.take<double>(FU * B) : nullptr;  double* a_us = useq ? bp.take<double>(FU * B) : nullptr;
+    double* s_xp = xpred ? bp.take<double>(FX * B) : nullptr; double* a_xp = xpred ? bp.take<double>(FX * B) : nullptr;
+    int32_t* d_sc = bp.take<int32_t>(B); int32_t* d_st = bp.take<int32_t>(B);
+    int32_t* d_it = bp.take<int32_t>(B); int32_t* d_sl = bp.take<int32_t>(B);
+    cudaStream_t s = c->stream;
+    B2C_CUDA(cudaMemcpyAsync(a_x0, x0, (size_t)B * 3 * 8, cudaMemcpyHostToDevice, s));
+    B2C_CUDA(cudaMemcpyAsync(a_xr, xref, (size_t)B * FX * 8, cudaMemcpyHostToDevice, s));
+    B2C_CUDA(cudaMemcpyAsync(a_ur, uref, (size_t)B * FU * 8, cudaMemcpyHostToDevice, s));
+    if (FO) B2C_CUDA(cudaMemcpyAsync(a_ob, obs, (size_t)B * FO * 8, cudaMemcpyHostToDevice, s));
+    if (step_count) B2C_CUDA(cudaMemcpyAsync(d_sc, step_count, (size_t)B * 4, cudaMemcpyHostToDevice, s));
+    if ((rc = to_soa(c, B, 3, a_x0, s_x0))) return rc;
+    if ((rc = to_soa(c, B, FX, a_xr, s_xr))) return rc;
+    if ((rc = to_soa(c, B, FU, a_ur, s_ur))) return rc;
+    if ((rc = to_soa(c, B, FO, a_ob, s_ob))) return rc;
+    rc = b2c_mpc_dev(c, B, p, s_x0, s_xr, s_ur, s_ob, step_count ? d_sc : nullptr,
+                     s_u0, d_cost, d_st, d_it, d_sl, s_us, s_xp);
+    if (rc) return rc;
+    if ((rc = to_aos(c, B, 2, s_u0, a_u0))) return rc;
+    B2C_CUDA(cudaMemcpyAsync(u0, a_u0, (size_t)B * 2 * 8, cudaMemcpyDeviceToHost, s));
+    B2C_CUDA(cudaMemcpyAsync(cost, d_cost, (size_t)B * 8, cudaMemcpyDeviceToHost, s));
+    if (useq) {
+        if ((rc = to_aos(c, B, FU, s_us, a_us))) return rc;
+        B2C_CUDA(cudaMemcpyAsync(useq, a_us, (size_t)B * FU * 8, cudaMemcpyDeviceToHost, s));
+    }
+    if (xpred) {
+        if ((rc = to_aos(c, B, FX, s_xp, a_xp))) return rc;
+        B2C_CUDA(cudaMemcpyAsync(xpred, a_xp, (size_t)B * FX * 8, cudaMemcpyDeviceToHost, s));
+    }
+    if (status) B2C_CUDA(cudaMemcpyAsync(status, d_st, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    if (iters) B2C_CUDA(cudaMemcpyAsync(iters, d_it, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    if (slack_used) B2C_CUDA(cudaMemcpyAsync(slack_used, d_sl, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    if (step_count) B2C_CUDA(cudaMemcpyAsync(step_count, d_sc, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    B2C_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+// ---- FMA peak microbenchmark (FP64 / FP32 roofline denominators) ------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_fma_peak(T* out, int iters, T a, T b) {
+    T x0 = (T)threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+            x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+        }
+    }
+    T s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == (T)123456789) out[0] = s;     // never true; keeps the chain alive
+}
+
+int b2c_measure_fma_peak(b2c_ctx* c, int bits, double* tflops) {
+    if (!c || !tflops) { b2c_set_error("null argument"); return -1; }
+    B2C_CUDA(cudaSetDevice(c->device));
+    int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, 4096, false);
+    if (rc) return rc;
+    const int iters = 4096, blocks = c->sm_count * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    B2C_CUDA(cudaEventCreate(&e0)); B2C_CUDA(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        B2C_CUDA(cudaEventRecord(e0, c->stream));
+        if (bits == 64) k_fma_peak<double><<<blocks, threads, 0, c->stream>>>((double*)c->dstage, iters, 0.999999, 1e-6);
+        else            k_fma_peak<float><<<blocks, threads, 0, c->stream>>>((float*)c->dstage, iters, 0.9999f, 1e-4f);
+        B2C_CHECK_LAUNCH(c);
+        B2C_CUDA(cudaEventRecord(e1, c->stream));
+        B2C_CUDA(cudaEventSynchronize(e1));
+        float ms = 0; B2C_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    double flops = 2.0 * 64.0 * (double)iters * (double)blocks * (double)threads;
+    *tflops = flops / (best * 1e-3) / 1e12;
+    return 0;
+}

@@ -1,0 +1,65 @@
+// Shared internals of libb2c.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include "b2c.h"
+
+struct b2c_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    // device scratch (grown on demand, never shrunk)
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    // device staging for the *_host entry points
+    void* dstage = nullptr;
+    size_t dstage_bytes = 0;
+    // pinned host staging
+    void* hstage = nullptr;
+    size_t hstage_bytes = 0;
+    int64_t launches = 0;
+};
+
+void b2c_set_error(const std::string& s);
+int b2c_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define B2C_CUDA(expr)                                                          \
+    do {                                                                        \
+        cudaError_t _e = (expr);                                                \
+        if (_e != cudaSuccess) return b2c_cuda_fail(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define B2C_CHECK_LAUNCH(ctx)                                                   \
+    do {                                                                        \
+        (ctx)->launches++;                                                      \
+        cudaError_t _e = cudaGetLastError();                                    \
+        if (_e != cudaSuccess) return b2c_cuda_fail(_e, "kernel launch", __FILE__, __LINE__); \
+    } while (0)
+
+int b2c_reserve(void** p, size_t* cur, size_t need, bool pinned_host);
+
+static inline int b2c_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+// ---- device helpers -------------------------------------------------------------------------
+// low-speed guards of the reference (lqr_controller.py:120-122, mpc_controller.py:186,425)
+__device__ __forceinline__ double b2c_guard_v(double v, int guard) {
+    if (guard == B2C_GUARD_LQR) return (fabs(v) < 1e-6) ? 0.01 : v;
+    if (guard == B2C_GUARD_MPC) return (fabs(v) > 0.01) ? v : 0.1;
+    return v;
+}
+
+// closed-interval wrap by +-2pi steps (lqr_controller.py:244-250): pi stays pi, -pi stays -pi.
+__device__ __forceinline__ double b2c_wrap(double a) {
+    const double PI = 3.141592653589793, TWO_PI = 2.0 * 3.141592653589793;
+    if (!(fabs(a) < 1e9)) return a;  // non-finite / absurd: leave (the reference would spin)
+    while (a > PI) a -= TWO_PI;
+    while (a < -PI) a += TWO_PI;
+    return a;
+}
+
+__device__ __forceinline__ double b2c_clip(double x, double lo, double hi) {
+    return fmin(fmax(x, lo), hi);   // NaN-propagation differs from np.clip only for NaN input
+}

@@ -1,0 +1,523 @@
+// K3: batched MPC QP.  One thread per instance; projected semismooth Newton whose linear solve is
+// a 3-state / 2-input Riccati sweep held in registers; per-stage data in coalesced SoA scratch.
+//
+// Reference problem (HC/controllers/mpc_controller.py:345-522 solve_with_ltv, :150-314 solve):
+//   min  sum_k [ (z_k-zc_k)'Q(z_k-zc_k) + (w_j+uo_k)'R(w_j+uo_k) ] + (z_N-zc_N)'P(z_N-zc_N) + rho*sum s^2
+//   s.t. z_{k+1} = A_k z_k + B_k w_{j(k)},  j(k) = min(k / block_size, Nb-1)
+//        -umax <= w_j + uo_k <= umax,   n_km.(p_k - o_m) >= d_safe + r_m - s_km,  s >= 0
+//   LTV: z = x - x_ref (error), w = du, uo_k = u_ref,k, zc = 0      LTI: z = x, w = u, uo = 0, zc = x_ref
+// Method: the slack of each soft row is eliminated in closed form,
+//   min_{s>=0} rho s^2  s.t. s >= g   ==   rho * max(0, g)^2 ,
+// which leaves a strictly convex, C^1, piecewise-quadratic optimal-control problem with bounds on
+// the inputs only.  Each Newton iteration = backward Riccati sweep on the current active sets
+// (violated rows add rho*n n' to the stage Hessian; inputs held at a bound by the sign of the true
+// gradient are frozen) + a forward roll-out with feedback, clipping and a monotone line search.
+// When the active sets stop changing the step lands on the exact minimiser (to rounding), i.e. the
+// same point CVXPY/OSQP approximates to 1e-5; typical count is 1-8 iterations.
+#include "b2c_common.cuh"
+
+namespace {
+
+struct MpcArgs {
+    int64_t B;
+    int kind, N, M, bs, Nb, max_iter, ramp_up_steps, soft;
+    double q0, q1, q2, r0, r1, p0, p1, p2;
+    double d_safe, rho, v_max, w_max, dt, tol;
+    const double* __restrict__ x0;
+    const double* __restrict__ xref;
+    const double* __restrict__ uref;
+    const double* __restrict__ obs;
+    int32_t* step_count;
+    double* u0; double* cost; int32_t* status; int32_t* iters; int32_t* slack_used;
+    double* useq; double* xpred;
+    double* scratch;
+};
+
+// scratch field map (each field is a length-B column; instance i lives at field*B + i)
+template <bool BS1> struct Lay {
+    static constexpr int MODEL = BS1 ? 8 : 28;
+    __host__ __device__ static int ab(int k) { return 4 * k; }                       // a,b,c,s
+    __host__ __device__ static int w(int N, int Nb, int buf, int j) { return 4 * N + buf * 2 * Nb + 2 * j; }
+    __host__ __device__ static int model(int N, int Nb, int j) { return 4 * N + 4 * Nb + MODEL * j; }
+    __host__ __device__ static int gain(int N, int Nb, int j) { return 4 * N + 4 * Nb + MODEL * Nb + 8 * j; }
+    __host__ __device__ static int total(int N, int Nb) { return 4 * N + 4 * Nb + (MODEL + 8) * Nb; }
+};
+
+#define SC(f) a.scratch[(int64_t)(f) * a.B + i]
+
+// np.unwrap step (numpy/lib/function_base.py semantics, period 2pi, discont pi)
+__device__ __forceinline__ double unwrap_correction(double dd) {
+    const double PI = 3.141592653589793, TWO_PI = 6.283185307179586;
+    double m = fmod(dd + PI, TWO_PI);
+    if (m < 0.0) m += TWO_PI;                 // python-style modulo
+    double ddmod = m - PI;
+    if (ddmod == -PI && dd > 0.0) ddmod = PI;
+    double corr = ddmod - dd;
+    if (fabs(dd) < PI) corr = 0.0;
+    return corr;
+}
+
+// ----- forward pass ---------------------------------------------------------------------------
+// Rolls the plant out from z0 under either the current inputs (USE_GAIN=false) or the Newton
+// update  w+ = clip(w - alpha*kf - K (z+ - z))  (USE_GAIN=true, written to buffer `dst`), and
+// accumulates cost + the per-super-stage quadratic model at the NEW trajectory.
+template <bool BS1, bool USE_GAIN>
+__device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, double z0t,
+                                              int src, int dst, double alpha, double& max_viol,
+                                              bool& infeasible, double& lamx, double& lamy, double& lamt) {
+    using L = Lay<BS1>;
+    const int N = a.N, Nb = a.Nb, M = a.M;
+    const bool ltv = (a.kind == B2C_MPC_LTV);
+    double zx = z0x, zy = z0y, zt = z0t;          // new trajectory
+    double ox_ = z0x, oy_ = z0y, ot_ = z0t;       // old trajectory (only with gains)
+    double J = 0.0;
+    max_viol = 0.0;
+    for (int j = 0; j < Nb; ++j) {
+        const int k_begin = j * a.bs;
+        const int k_end = (j == Nb - 1) ? N : (k_begin + a.bs);
+        // bounds of this block: intersection over its steps of [-umax - uo_k, umax - uo_k]
+        double lb0 = -a.v_max, ub0 = a.v_max, lb1 = -a.w_max, ub1 = a.w_max;
+        if (ltv) {
+            lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
+            for (int k = k_begin; k < k_end; ++k) {
+                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
+                lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
+            }
+        }
+        if (lb0 > ub0 || lb1 > ub1) infeasible = true;
+        double w0, w1, wo0 = 0.0, wo1 = 0.0;
+        if (USE_GAIN) {
+            wo0 = SC(L::w(N, Nb, src, j)); wo1 = SC(L::w(N, Nb, src, j) + 1);
+            const int g = L::gain(N, Nb, j);
+            double dx = zx - ox_, dy = zy - oy_, dt_ = zt - ot_;
+            w0 = wo0 - alpha * SC(g + 6) - (SC(g + 0) * dx + SC(g + 1) * dy + SC(g + 2) * dt_);
+            w1 = wo1 - alpha * SC(g + 7) - (SC(g + 3) * dx + SC(g + 4) * dy + SC(g + 5) * dt_);
+            w0 = b2c_clip(w0, lb0, ub0); w1 = b2c_clip(w1, lb1, ub1);
+            SC(L::w(N, Nb, dst, j)) = w0; SC(L::w(N, Nb, dst, j) + 1) = w1;
+        } else {
+            w0 = SC(L::w(N, Nb, src, j)); w1 = SC(L::w(N, Nb, src, j) + 1);
+        }
+        // block accumulators (only the general path needs them)
+        double al = 0.0, be = 0.0;                             // Phi = I + [0 0 al; 0 0 be; 0 0 0]
+        double g00 = 0.0, g01 = 0.0, g10 = 0.0, g11 = 0.0, g21 = 0.0;   // Gamma (3x2), Gamma[2][0] == 0
+        double Hzz[6] = {0, 0, 0, 0, 0, 0};                    // 00 01 02 11 12 22
+        double Hzu[6] = {0, 0, 0, 0, 0, 0};                    // row-major 3x2
+        double Huu[3] = {0, 0, 0};                             // 00 01 11
+        double gz[3] = {0, 0, 0}, gu[2] = {0, 0};
+        for (int k = k_begin; k < k_end; ++k) {
+            double ex = zx, ey = zy, et = zt, uo0 = 0.0, uo1 = 0.0;
+            const double prx = __ldg(a.xref + (int64_t)(3 * k) * a.B + i);
+            const double pry = __ldg(a.xref + (int64_t)(3 * k + 1) * a.B + i);
+            if (ltv) {
+                uo0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
+                uo1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+            } else {
+                ex -= prx; ey -= pry; et -= __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+            }
+            double wxx = a.q0, wxy = 0.0, wyy = a.q1;
+            double gx = a.q0 * ex, gy = a.q1 * ey, gt = a.q2 * et;
+            J += a.q0 * ex * ex + a.q1 * ey * ey + a.q2 * et * et;
+            for (int m = 0; m < M; ++m) {                      // soft obstacle rows, :439-468 / :238-270
+                const double obx = __ldg(a.obs + (int64_t)(3 * m) * a.B + i);
+                const double oby = __ldg(a.obs + (int64_t)(3 * m + 1) * a.B + i);
+                const double obr = __ldg(a.obs + (int64_t)(3 * m + 2) * a.B + i);
+                const double ddx = prx - obx, ddy = pry - oby;
+                const double d2 = ddx * ddx + ddy * ddy;
+                if (d2 > 1e-4) {                               // dist > 0.01
+                    const double inv = rsqrt(d2);
+                    const double nx = ddx * inv, ny = ddy * inv;
+                    // LTV: p = p_ref + dz  => n.(p - o) = dist + n.dz ;  LTI: p = z
+                    double lhs = ltv ? (d2 * inv + nx * zx + ny * zy) : (nx * (zx - obx) + ny * (zy - oby));
+                    double viol = (a.d_safe + obr) - lhs;
+                    if (viol > 0.0) {
+                        max_viol = fmax(max_viol, viol);
+                        J += a.rho * viol * viol;
+                        const double rn0 = a.rho * nx, rn1 = a.rho * ny;
+                        wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
+                        gx -= rn0 * viol; gy -= rn1 * viol;
+                    }
+                }
+            }
+            const double ut0 = w0 + uo0, ut1 = w1 + uo1;
+            J += a.r0 * ut0 * ut0 + a.r1 * ut1 * ut1;
+            const double a_k = SC(L::ab(k)), b_k = SC(L::ab(k) + 1), c_k = SC(L::ab(k) + 2), s_k = SC(L::ab(k) + 3);
+            if (BS1) {
+                const int mo = L::model(N, Nb, j);
+                SC(mo + 0) = gx; SC(mo + 1) = gy; SC(mo + 2) = gt;
+                SC(mo + 3) = wxx; SC(mo + 4) = wxy; SC(mo + 5) = wyy;
+                SC(mo + 6) = a.r0 * ut0; SC(mo + 7) = a.r1 * ut1;
+            } else {
+                const double t0 = wxx * al + wxy * be, t1 = wxy * al + wyy * be;
+                Hzz[0] += wxx; Hzz[1] += wxy; Hzz[2] += t0; Hzz[3] += wyy; Hzz[4] += t1;
+                Hzz[5] += al * t0 + be * t1 + a.q2;
+                const double wg00 = wxx * g00 + wxy * g10, wg01 = wxx * g01 + wxy * g11;
+                const double wg10 = wxy * g00 + wyy * g10, wg11 = wxy * g01 + wyy * g11;
+                const double wg21 = a.q2 * g21;
+                Hzu[0] += wg00; Hzu[1] += wg01; Hzu[2] += wg10; Hzu[3] += wg11;
+                Hzu[4] += al * wg00 + be * wg10; Hzu[5] += al * wg01 + be * wg11 + wg21;
+                Huu[0] += g00 * wg00 + g10 * wg10 + a.r0;
+                Huu[1] += g00 * wg01 + g10 * wg11;
+                Huu[2] += g01 * wg01 + g11 * wg11 + g21 * wg21 + a.r1;
+                gz[0] += gx; gz[1] += gy; gz[2] += al * gx + be * gy + gt;
+                gu[0] += g00 * gx + g10 * gy + a.r0 * ut0;
+                gu[1] += g01 * gx + g11 * gy + g21 * gt + a.r1 * ut1;
+                // Gamma <- A_k Gamma + B_k ; Phi <- A_k Phi
+                g01 += a_k * g21; g11 += b_k * g21;
+                g00 += c_k; g10 += s_k; g21 += a.dt;
+                al += a_k; be += b_k;
+            }
+            // advance plant(s)
+            const double nzx = zx + a_k * zt + c_k * w0, nzy = zy + b_k * zt + s_k * w0;
+            zt = zt + a.dt * w1; zx = nzx; zy = nzy;
+            if (USE_GAIN) {
+                const double nox = ox_ + a_k * ot_ + c_k * wo0, noy = oy_ + b_k * ot_ + s_k * wo0;
+                ot_ = ot_ + a.dt * wo1; ox_ = nox; oy_ = noy;
+            }
+        }
+        if (!BS1) {
+            const int mo = L::model(N, Nb, j);
+#pragma unroll
+            for (int e = 0; e < 6; e++) SC(mo + e) = Hzz[e];
+#pragma unroll
+            for (int e = 0; e < 6; e++) SC(mo + 6 + e) = Hzu[e];
+            SC(mo + 12) = Huu[0]; SC(mo + 13) = Huu[1]; SC(mo + 14) = Huu[2];
+            SC(mo + 15) = gz[0]; SC(mo + 16) = gz[1]; SC(mo + 17) = gz[2];
+            SC(mo + 18) = gu[0]; SC(mo + 19) = gu[1];
+            SC(mo + 20) = al; SC(mo + 21) = be;
+            SC(mo + 22) = g00; SC(mo + 23) = g01; SC(mo + 24) = g10; SC(mo + 25) = g11; SC(mo + 26) = g21;
+        }
+    }
+    // terminal cost (mpc_controller.py:412 / :212-213)
+    double ex = zx, ey = zy, et = zt;
+    if (!ltv) {
+        ex -= __ldg(a.xref + (int64_t)(3 * N) * a.B + i);
+        ey -= __ldg(a.xref + (int64_t)(3 * N + 1) * a.B + i);
+        et -= __ldg(a.xref + (int64_t)(3 * N + 2) * a.B + i);
+    }
+    J += a.p0 * ex * ex + a.p1 * ey * ey + a.p2 * et * et;
+    lamx = a.p0 * ex; lamy = a.p1 * ey; lamt = a.p2 * et;
+    return J;
+}
+
+// ----- backward pass --------------------------------------------------------------------------
+// Riccati sweep on the stored model.  Returns the Newton decrement 1/2 sum qu' Quu^-1 qu.
+template <bool BS1>
+__device__ __forceinline__ double mpc_backward(const MpcArgs& a, int64_t i, int cur,
+                                               double lamx, double lamy, double lamt) {
+    using L = Lay<BS1>;
+    const int N = a.N, Nb = a.Nb;
+    const bool ltv = (a.kind == B2C_MPC_LTV);
+    // value function 1/2 dz'S dz + sv'dz  and the true costate lam
+    double s00 = a.p0, s01 = 0.0, s02 = 0.0, s11 = a.p1, s12 = 0.0, s22 = a.p2;
+    double v0 = lamx, v1 = lamy, v2 = lamt;
+    double l0 = lamx, l1 = lamy, l2 = lamt;
+    double dec = 0.0;
+    for (int j = Nb - 1; j >= 0; --j) {
+        const int mo = L::model(N, Nb, j);
+        double Hzz0, Hzz1, Hzz2, Hzz3, Hzz4, Hzz5, Hzu0, Hzu1, Hzu2, Hzu3, Hzu4, Hzu5, Huu0, Huu1, Huu2;
+        double gz0, gz1, gz2, gu0, gu1, al, be, g00, g01, g10, g11, g21;
+        if (BS1) {
+            gz0 = SC(mo + 0); gz1 = SC(mo + 1); gz2 = SC(mo + 2);
+            Hzz0 = SC(mo + 3); Hzz1 = SC(mo + 4); Hzz3 = SC(mo + 5);
+            Hzz2 = 0.0; Hzz4 = 0.0; Hzz5 = a.q2;
+            Hzu0 = Hzu1 = Hzu2 = Hzu3 = Hzu4 = Hzu5 = 0.0;
+            Huu0 = a.r0; Huu1 = 0.0; Huu2 = a.r1;
+            gu0 = SC(mo + 6); gu1 = SC(mo + 7);
+            al = SC(L::ab(j)); be = SC(L::ab(j) + 1);
+            g00 = SC(L::ab(j) + 2); g10 = SC(L::ab(j) + 3); g01 = 0.0; g11 = 0.0; g21 = a.dt;
+        } else {
+            Hzz0 = SC(mo + 0); Hzz1 = SC(mo + 1); Hzz2 = SC(mo + 2); Hzz3 = SC(mo + 3); Hzz4 = SC(mo + 4); Hzz5 = SC(mo + 5);
+            Hzu0 = SC(mo + 6); Hzu1 = SC(mo + 7); Hzu2 = SC(mo + 8); Hzu3 = SC(mo + 9); Hzu4 = SC(mo + 10); Hzu5 = SC(mo + 11);
+            Huu0 = SC(mo + 12); Huu1 = SC(mo + 13); Huu2 = SC(mo + 14);
+            gz0 = SC(mo + 15); gz1 = SC(mo + 16); gz2 = SC(mo + 17);
+            gu0 = SC(mo + 18); gu1 = SC(mo + 19);
+            al = SC(mo + 20); be = SC(mo + 21);
+            g00 = SC(mo + 22); g01 = SC(mo + 23); g10 = SC(mo + 24); g11 = SC(mo + 25); g21 = SC(mo + 26);
+        }
+        // true gradient wrt w_j (decides which bounded inputs are frozen), then costate update
+        const double gt0 = gu0 + g00 * l0 + g10 * l1;
+        const double gt1 = gu1 + g01 * l0 + g11 * l1 + g21 * l2;
+        {
+            const double nl2 = gz2 + al * l0 + be * l1 + l2;
+            l0 = gz0 + l0; l1 = gz1 + l1; l2 = nl2;
+        }
+        // bounds of the block (same rule as the forward pass)
+        double lb0 = -a.v_max, ub0 = a.v_max, lb1 = -a.w_max, ub1 = a.w_max;
+        if (ltv) {
+            const int k_begin = j * a.bs, k_end = (j == Nb - 1) ? N : (k_begin + a.bs);
+            lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
+            for (int k = k_begin; k < k_end; ++k) {
+                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
+                lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
+            }
+        }
+        const double w0 = SC(L::w(N, Nb, cur, j)), w1 = SC(L::w(N, Nb, cur, j) + 1);
+        const bool c0 = (w0 <= lb0 && gt0 > 0.0) || (w0 >= ub0 && gt0 < 0.0);
+        const bool c1 = (w1 <= lb1 && gt1 > 0.0) || (w1 >= ub1 && gt1 < 0.0);
+        // SA = S * Abar : first two columns are S's, third is t
+        const double t0 = al * s00 + be * s01 + s02;
+        const double t1 = al * s01 + be * s11 + s12;
+        const double t2 = al * s02 + be * s12 + s22;
+        // Qzz = Hzz + Abar' S Abar
+        const double Q00 = Hzz0 + s00, Q01 = Hzz1 + s01, Q02 = Hzz2 + t0;
+        const double Q11 = Hzz3 + s11, Q12 = Hzz4 + t1;
+        const double Q22 = Hzz5 + al * t0 + be * t1 + t2;
+        // Quz = Hzu' + Bbar' S Abar   (2x3)
+        double U00 = Hzu0 + g00 * s00 + g10 * s01;
+        double U01 = Hzu2 + g00 * s01 + g10 * s11;
+        double U02 = Hzu4 + g00 * t0 + g10 * t1;
+        double U10 = Hzu1 + g01 * s00 + g11 * s01 + g21 * s02;
+        double U11 = Hzu3 + g01 * s01 + g11 * s11 + g21 * s12;
+        double U12 = Hzu5 + g01 * t0 + g11 * t1 + g21 * t2;
+        // Quu = Huu + Bbar' S Bbar
+        const double sb00 = s00 * g00 + s01 * g10, sb10 = s01 * g00 + s11 * g10, sb20 = s02 * g00 + s12 * g10;
+        const double sb01 = s00 * g01 + s01 * g11 + s02 * g21;
+        const double sb11 = s01 * g01 + s11 * g11 + s12 * g21;
+        const double sb21 = s02 * g01 + s12 * g11 + s22 * g21;
+        double R00 = Huu0 + g00 * sb00 + g10 * sb10;
+        double R01 = Huu1 + g00 * sb01 + g10 * sb11;
+        double R11 = Huu2 + g01 * sb01 + g11 * sb11 + g21 * sb21;
+        (void)sb20;
+        // qz, qu
+        const double qz0 = gz0 + v0, qz1 = gz1 + v1, qz2 = gz2 + al * v0 + be * v1 + v2;
+        double qu0 = gu0 + g00 * v0 + g10 * v1;
+        double qu1 = gu1 + g01 * v0 + g11 * v1 + g21 * v2;
+        if (c0) { R00 = 1.0; R01 = 0.0; U00 = 0.0; U01 = 0.0; U02 = 0.0; qu0 = 0.0; }
+        if (c1) { R11 = 1.0; R01 = 0.0; U10 = 0.0; U11 = 0.0; U12 = 0.0; qu1 = 0.0; }
+        const double idet = 1.0 / (R00 * R11 - R01 * R01);
+        const double i00 = R11 * idet, i01 = -R01 * idet, i11 = R00 * idet;
+        const double K00 = i00 * U00 + i01 * U10, K01 = i00 * U01 + i01 * U11, K02 = i00 * U02 + i01 * U12;
+        const double K10 = i01 * U00 + i11 * U10, K11 = i01 * U01 + i11 * U11, K12 = i01 * U02 + i11 * U12;
+        const double k0 = i00 * qu0 + i01 * qu1, k1 = i01 * qu0 + i11 * qu1;
+        const int g = L::gain(N, Nb, j);
+        SC(g + 0) = K00; SC(g + 1) = K01; SC(g + 2) = K02; SC(g + 3) = K10; SC(g + 4) = K11; SC(g + 5) = K12;
+        SC(g + 6) = k0; SC(g + 7) = k1;
+        dec += 0.5 * (qu0 * k0 + qu1 * k1);
+        // S = Qzz - Quz' K ; sv = qz - Quz' kf
+        s00 = Q00 - (U00 * K00 + U10 * K10);
+        s01 = Q01 - (U00 * K01 + U10 * K11);
+        s02 = Q02 - (U00 * K02 + U10 * K12);
+        s11 = Q11 - (U01 * K01 + U11 * K11);
+        s12 = Q12 - (U01 * K02 + U11 * K12);
+        s22 = Q22 - (U02 * K02 + U12 * K12);
+        v0 = qz0 - (U00 * k0 + U10 * k1);
+        v1 = qz1 - (U01 * k0 + U11 * k1);
+        v2 = qz2 - (U02 * k0 + U12 * k1);
+    }
+    return dec;
+}
+
+// ----- the solver kernel -----------------------------------------------------------------------
+#define MPC_TPB 128
+#define MPC_LS_MAX 14
+
+template <bool BS1>
+__global__ void __launch_bounds__(MPC_TPB)
+k_mpc(const MpcArgs a) {
+    using L = Lay<BS1>;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.B) return;
+    const int N = a.N, Nb = a.Nb;
+    const bool ltv = (a.kind == B2C_MPC_LTV);
+
+    // ---- setup: linearize along the reference (K1 fused), initial state, initial inputs -------
+    const double x0x = __ldg(a.x0 + i), x0y = __ldg(a.x0 + a.B + i), x0t = __ldg(a.x0 + 2 * a.B + i);
+    const double r0x = __ldg(a.xref + i), r0y = __ldg(a.xref + a.B + i), r0t = __ldg(a.xref + 2 * a.B + i);
+    double z0x, z0y, z0t;
+    if (ltv) {                                    // mpc_controller.py:392-401, :421
+        z0x = x0x - r0x; z0y = x0y - r0y; z0t = b2c_wrap(x0t - r0t);
+        double th_prev = r0t, cum = 0.0;          // np.unwrap along the horizon
+        for (int k = 0; k < N; ++k) {
+            const double th_raw = __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+            if (k > 0) cum += unwrap_correction(th_raw - th_prev);
+            th_prev = th_raw;
+            const double th = th_raw + cum;
+            const double vr = b2c_guard_v(__ldg(a.uref + (int64_t)(2 * k) * a.B + i), B2C_GUARD_MPC);   // :425
+            double s, c; sincos(th, &s, &c);
+            SC(L::ab(k) + 0) = -vr * s * a.dt; SC(L::ab(k) + 1) = vr * c * a.dt;
+            SC(L::ab(k) + 2) = c * a.dt;       SC(L::ab(k) + 3) = s * a.dt;
+        }
+        for (int j = 0; j < Nb; ++j) { SC(L::w(N, Nb, 0, j)) = 0.0; SC(L::w(N, Nb, 0, j) + 1) = 0.0; }
+    } else {                                      // :186-190, :223
+        z0x = x0x; z0y = x0y; z0t = x0t;
+        const double vr = b2c_guard_v(__ldg(a.uref + i), B2C_GUARD_MPC);
+        double s, c; sincos(r0t, &s, &c);
+        for (int k = 0; k < N; ++k) {
+            SC(L::ab(k) + 0) = -vr * s * a.dt; SC(L::ab(k) + 1) = vr * c * a.dt;
+            SC(L::ab(k) + 2) = c * a.dt;       SC(L::ab(k) + 3) = s * a.dt;
+            SC(L::w(N, Nb, 0, k)) = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
+            SC(L::w(N, Nb, 0, k) + 1) = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+        }
+    }
+    // clip the initial inputs into their boxes (bounds recomputed exactly as in the passes)
+    bool infeasible = false;
+    for (int j = 0; j < Nb; ++j) {
+        double lb0 = -a.v_max, ub0 = a.v_max, lb1 = -a.w_max, ub1 = a.w_max;
+        if (ltv) {
+            const int k_begin = j * a.bs, k_end = (j == Nb - 1) ? N : (k_begin + a.bs);
+            lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
+            for (int k = k_begin; k < k_end; ++k) {
+                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
+                lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
+            }
+        }
+        if (lb0 > ub0 || lb1 > ub1) infeasible = true;
+        SC(L::w(N, Nb, 0, j)) = b2c_clip(SC(L::w(N, Nb, 0, j)), lb0, ub0);
+        SC(L::w(N, Nb, 0, j) + 1) = b2c_clip(SC(L::w(N, Nb, 0, j) + 1), lb1, ub1);
+    }
+
+    // ---- Newton loop (state machine so that a warp's lanes share each pass) --------------------
+    int cur = 0, it = 0, st = B2C_MAXITER;
+    double lamx, lamy, lamt, max_viol = 0.0;
+    double J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, infeasible, lamx, lamy, lamt);
+    bool active = true;
+    if (infeasible) { st = B2C_INFEASIBLE; active = false; }
+    if (!(fabs(J) < 1e300)) { st = B2C_NONFINITE; active = false; }
+    bool need_backward = true;
+    double alpha = 1.0, dec = 0.0;
+    int ls = 0;
+    while (active) {
+        if (need_backward) {
+            dec = mpc_backward<BS1>(a, i, cur, lamx, lamy, lamt);
+            if (!(dec < 1e300)) { st = B2C_NONFINITE; break; }
+            if (dec <= a.tol * fmax(1.0, fabs(J))) { st = B2C_OK; break; }
+            if (it >= a.max_iter) { st = B2C_MAXITER; break; }
+            ++it; alpha = 1.0; ls = 0; need_backward = false;
+        }
+        double tlx, tly, tlt, tviol;
+        bool dummy = false;
+        const double Jn = mpc_forward<BS1, true>(a, i, z0x, z0y, z0t, cur, cur ^ 1, alpha, tviol, dummy, tlx, tly, tlt);
+        if (Jn < J) {
+            J = Jn; cur ^= 1; lamx = tlx; lamy = tly; lamt = tlt; max_viol = tviol; need_backward = true;
+        } else {
+            alpha *= 0.5;
+            if (++ls >= MPC_LS_MAX) {             // cannot decrease any further: rounding floor or stall
+                st = (dec <= 1e-9 * fmax(1.0, fabs(J))) ? B2C_OK : B2C_MAXITER;
+                break;
+            }
+        }
+    }
+
+    // ---- outputs ---------------------------------------------------------------------------------
+    const double ur00 = __ldg(a.uref + i), ur01 = __ldg(a.uref + a.B + i);
+    double u00, u01, Jout;
+    int sc = a.step_count ? a.step_count[i] : a.ramp_up_steps;
+    if (st == B2C_OK) {
+        const double w0 = SC(L::w(N, Nb, cur, 0)), w1 = SC(L::w(N, Nb, cur, 0) + 1);
+        u00 = ltv ? (ur00 + w0) : w0;
+        u01 = ltv ? (ur01 + w1) : w1;
+        Jout = J;
+        if (a.useq || a.xpred) {                 // :484-498: un-block, add the (wrapped) references
+            double zx = z0x, zy = z0y, zt = z0t;
+            for (int k = 0; k <= N; ++k) {
+                if (a.xpred) {
+                    double ax = zx, ay = zy, at = zt;
+                    if (ltv) {
+                        ax += __ldg(a.xref + (int64_t)(3 * k) * a.B + i);
+                        ay += __ldg(a.xref + (int64_t)(3 * k + 1) * a.B + i);
+                        at += __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+                    }
+                    a.xpred[(int64_t)(3 * k) * a.B + i] = ax;
+                    a.xpred[(int64_t)(3 * k + 1) * a.B + i] = ay;
+                    a.xpred[(int64_t)(3 * k + 2) * a.B + i] = at;
+                }
+                if (k == N) break;
+                int j = k / a.bs; if (j > Nb - 1) j = Nb - 1;
+                const double wk0 = SC(L::w(N, Nb, cur, j)), wk1 = SC(L::w(N, Nb, cur, j) + 1);
+                if (a.useq) {
+                    a.useq[(int64_t)(2 * k) * a.B + i] = ltv ? (wk0 + __ldg(a.uref + (int64_t)(2 * k) * a.B + i)) : wk0;
+                    a.useq[(int64_t)(2 * k + 1) * a.B + i] = ltv ? (wk1 + __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i)) : wk1;
+                }
+                const double a_k = SC(L::ab(k)), b_k = SC(L::ab(k) + 1), c_k = SC(L::ab(k) + 2), s_k = SC(L::ab(k) + 3);
+                const double nzx = zx + a_k * zt + c_k * wk0, nzy = zy + b_k * zt + s_k * wk0;
+                zt = zt + a.dt * wk1; zx = nzx; zy = nzy;
+            }
+        }
+        if (ltv) {                                // cold-start ramp, :500-507
+            if (sc < a.ramp_up_steps) {
+                const double lim = a.w_max * ((double)(sc + 1) / (double)a.ramp_up_steps);
+                u01 = b2c_clip(u01, -lim, lim);
+                if (a.useq) a.useq[a.B + i] = u01;
+            }
+            if (a.step_count) a.step_count[i] = sc + 1;
+        }
+    } else {                                      // _get_fallback_solution, :316-343
+        const double e0 = x0x - r0x, e2 = b2c_wrap(x0t - r0t);
+        u00 = b2c_clip(ur00 + (-1.0 * e0), -a.v_max, a.v_max);
+        u01 = b2c_clip(ur01 + (-0.5 * e2), -a.w_max, a.w_max);
+        Jout = __longlong_as_double(0x7ff0000000000000LL);   // +inf
+        max_viol = 0.0;
+        for (int k = 0; k <= N; ++k) {
+            if (a.xpred) {
+                a.xpred[(int64_t)(3 * k) * a.B + i] = x0x;
+                a.xpred[(int64_t)(3 * k + 1) * a.B + i] = x0y;
+                a.xpred[(int64_t)(3 * k + 2) * a.B + i] = x0t;
+            }
+            if (k < N && a.useq) {
+                a.useq[(int64_t)(2 * k) * a.B + i] = u00;
+                a.useq[(int64_t)(2 * k + 1) * a.B + i] = u01;
+            }
+        }
+    }
+    a.u0[i] = u00; a.u0[a.B + i] = u01;
+    a.cost[i] = Jout;
+    if (a.status) a.status[i] = st;
+    if (a.iters) a.iters[i] = it;
+    if (a.slack_used) a.slack_used[i] = (max_viol > 1e-6) ? 1 : 0;   // :485 / :294-296
+}
+
+}  // namespace
+
+static int mpc_fields(const b2c_mpc_params* p) {
+    const int bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
+    const int Nb = (p->N + bs - 1) / bs;
+    return bs == 1 ? Lay<true>::total(p->N, Nb) : Lay<false>::total(p->N, Nb);
+}
+
+int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B) {
+    if (!p || B <= 0) return 0;
+    return (int64_t)mpc_fields(p) * B * (int64_t)sizeof(double);
+}
+
+int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
+                const double* x0, const double* xref, const double* uref, const double* obs,
+                int32_t* step_count,
+                double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                double* useq, double* xpred) {
+    if (!ctx || !p) { b2c_set_error("null context/params"); return -1; }
+    if (p->N < 1 || p->N > 4096 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
+    if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
+    if (!p->soft && p->M > 0) {
+        b2c_set_error("hard obstacle constraints (use_soft_constraints=False) are not implemented yet");
+        return -4;
+    }
+    if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
+    if (B <= 0) return 0;
+    MpcArgs a;
+    a.B = B; a.kind = p->kind; a.N = p->N; a.M = p->M;
+    a.bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
+    a.Nb = (a.N + a.bs - 1) / a.bs;
+    a.max_iter = p->max_iter > 0 ? p->max_iter : 60;
+    a.ramp_up_steps = p->ramp_up_steps; a.soft = p->soft;
+    a.q0 = p->Qd[0]; a.q1 = p->Qd[1]; a.q2 = p->Qd[2]; a.r0 = p->Rd[0]; a.r1 = p->Rd[1];
+    a.p0 = p->Pd[0]; a.p1 = p->Pd[1]; a.p2 = p->Pd[2];
+    a.d_safe = p->d_safe; a.rho = p->rho; a.v_max = p->v_max; a.w_max = p->w_max; a.dt = p->dt;
+    a.tol = p->tol > 0 ? p->tol : 1e-14;
+    a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
+    a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
+    a.useq = useq; a.xpred = xpred;
+    const size_t need = (size_t)b2c_mpc_scratch_bytes(p, B);
+    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, need, false);
+    if (rc) return rc;
+    a.scratch = (double*)ctx->scratch;
+    if (a.bs == 1) k_mpc<true><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    else           k_mpc<false><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    B2C_CHECK_LAUNCH(ctx);
+    return 0;
+}
