@@ -44,15 +44,29 @@ int b2c_reserve(void** p, size_t* cur, size_t need, bool pinned_host);
 static inline int b2c_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
 
 // ---- device helpers -------------------------------------------------------------------------
+// B2C_HD functions also compile for the host so that tests/ can run the *same* per-instance code
+// on the CPU (tools/emul, -DB2C_HOST_EMUL, a separate test-only library; libb2c.so never calls them
+// on the host and has no CPU path).
+#define B2C_HD __host__ __device__ __forceinline__
+#ifdef __CUDA_ARCH__
+#define B2C_LDG(p) __ldg(p)
+#define B2C_RSQRT(x) rsqrt(x)
+#define B2C_MUL(a, b) __dmul_rn((a), (b))
+#else
+#include <math.h>
+#define B2C_LDG(p) (*(p))
+#define B2C_RSQRT(x) (1.0 / sqrt(x))
+#define B2C_MUL(a, b) ((a) * (b))
+#endif
 // low-speed guards of the reference (lqr_controller.py:120-122, mpc_controller.py:186,425)
-__device__ __forceinline__ double b2c_guard_v(double v, int guard) {
+B2C_HD double b2c_guard_v(double v, int guard) {
     if (guard == B2C_GUARD_LQR) return (fabs(v) < 1e-6) ? 0.01 : v;
     if (guard == B2C_GUARD_MPC) return (fabs(v) > 0.01) ? v : 0.1;
     return v;
 }
 
 // closed-interval wrap by +-2pi steps (lqr_controller.py:244-250): pi stays pi, -pi stays -pi.
-__device__ __forceinline__ double b2c_wrap(double a) {
+B2C_HD double b2c_wrap(double a) {
     const double PI = 3.141592653589793, TWO_PI = 2.0 * 3.141592653589793;
     if (!(fabs(a) < 1e9)) return a;  // non-finite / absurd: leave (the reference would spin)
     while (a > PI) a -= TWO_PI;
@@ -60,6 +74,6 @@ __device__ __forceinline__ double b2c_wrap(double a) {
     return a;
 }
 
-__device__ __forceinline__ double b2c_clip(double x, double lo, double hi) {
+B2C_HD double b2c_clip(double x, double lo, double hi) {
     return fmin(fmax(x, lo), hi);   // NaN-propagation differs from np.clip only for NaN input
 }

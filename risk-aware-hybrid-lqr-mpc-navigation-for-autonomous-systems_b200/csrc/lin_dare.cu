@@ -16,7 +16,7 @@ struct LinModel {
     double adiag;             // 1 (discrete) or 0 (continuous Jacobian)
 };
 
-__device__ __forceinline__ LinModel b2c_linearize_point(double v, double th, double dt, int method) {
+B2C_HD LinModel b2c_linearize_point(double v, double th, double dt, int method) {
     double s, c;
     sincos(th, &s, &c);
     LinModel m;
@@ -24,15 +24,15 @@ __device__ __forceinline__ LinModel b2c_linearize_point(double v, double th, dou
         m.a13 = -v * s; m.a23 = v * c;
         m.b11 = c; m.b21 = s; m.b12 = 0.0; m.b22 = 0.0; m.b32 = 1.0; m.adiag = 0.0;
     } else {                                      // :98-118 == :190-225
-        m.a13 = __dmul_rn(__dmul_rn(-v, s), dt);
-        m.a23 = __dmul_rn(__dmul_rn(v, c), dt);
-        m.b11 = __dmul_rn(c, dt); m.b21 = __dmul_rn(s, dt);
+        m.a13 = B2C_MUL(B2C_MUL(-v, s), dt);
+        m.a23 = B2C_MUL(B2C_MUL(v, c), dt);
+        m.b11 = B2C_MUL(c, dt); m.b21 = B2C_MUL(s, dt);
         m.b12 = 0.0; m.b22 = 0.0; m.b32 = dt; m.adiag = 1.0;
         if (method == B2C_LIN_EXACT) {            // :120-158; A^2 = 0 => series terminates:
             // A_d = I + A dt,  B_d = B dt + A B dt^2/2
             double h = 0.5 * dt * dt;
-            m.b12 = __dmul_rn(__dmul_rn(-v, s), h);
-            m.b22 = __dmul_rn(__dmul_rn(v, c), h);
+            m.b12 = B2C_MUL(B2C_MUL(-v, s), h);
+            m.b22 = B2C_MUL(B2C_MUL(v, c), h);
         }
     }
     return m;
@@ -107,7 +107,7 @@ int b2c_linearize_packed_dev(b2c_ctx* ctx, int64_t B, int method, int guard, dou
 // Replaces scipy.linalg.solve_discrete_are (QZ on the symplectic pencil), lqr_controller.py:126.
 struct M3 { double m[9]; };
 
-__device__ __forceinline__ M3 m3_mul(const M3& a, const M3& b) {
+B2C_HD M3 m3_mul(const M3& a, const M3& b) {
     M3 r;
 #pragma unroll
     for (int i = 0; i < 3; i++)
@@ -116,7 +116,7 @@ __device__ __forceinline__ M3 m3_mul(const M3& a, const M3& b) {
             r.m[i * 3 + j] = fma(a.m[i * 3 + 2], b.m[6 + j], fma(a.m[i * 3 + 1], b.m[3 + j], a.m[i * 3] * b.m[j]));
     return r;
 }
-__device__ __forceinline__ M3 m3_mul_tn(const M3& a, const M3& b) {   // a' b
+B2C_HD M3 m3_mul_tn(const M3& a, const M3& b) {   // a' b
     M3 r;
 #pragma unroll
     for (int i = 0; i < 3; i++)
@@ -125,7 +125,7 @@ __device__ __forceinline__ M3 m3_mul_tn(const M3& a, const M3& b) {   // a' b
             r.m[i * 3 + j] = fma(a.m[6 + i], b.m[6 + j], fma(a.m[3 + i], b.m[3 + j], a.m[i] * b.m[j]));
     return r;
 }
-__device__ __forceinline__ M3 m3_mul_nt(const M3& a, const M3& b) {   // a b'
+B2C_HD M3 m3_mul_nt(const M3& a, const M3& b) {   // a b'
     M3 r;
 #pragma unroll
     for (int i = 0; i < 3; i++)
@@ -134,7 +134,7 @@ __device__ __forceinline__ M3 m3_mul_nt(const M3& a, const M3& b) {   // a b'
             r.m[i * 3 + j] = fma(a.m[i * 3 + 2], b.m[j * 3 + 2], fma(a.m[i * 3 + 1], b.m[j * 3 + 1], a.m[i * 3] * b.m[j * 3]));
     return r;
 }
-__device__ __forceinline__ M3 m3_inv(const M3& a) {
+B2C_HD M3 m3_inv(const M3& a) {
     double c00 = fma(a.m[4], a.m[8], -a.m[5] * a.m[7]);
     double c01 = fma(a.m[5], a.m[6], -a.m[3] * a.m[8]);
     double c02 = fma(a.m[3], a.m[7], -a.m[4] * a.m[6]);
@@ -152,23 +152,20 @@ __device__ __forceinline__ M3 m3_inv(const M3& a) {
     r.m[8] = fma(a.m[0], a.m[4], -a.m[1] * a.m[3]) * id;
     return r;
 }
-__device__ __forceinline__ void m3_symmetrize(M3& a) {
+B2C_HD void m3_symmetrize(M3& a) {
     double t;
     t = 0.5 * (a.m[1] + a.m[3]); a.m[1] = t; a.m[3] = t;
     t = 0.5 * (a.m[2] + a.m[6]); a.m[2] = t; a.m[6] = t;
     t = 0.5 * (a.m[5] + a.m[7]); a.m[5] = t; a.m[7] = t;
 }
 
-#define DARE_MAX_ITER 48
+#define DARE_MAX_ITER 33   // 2^33 steps: closed-loop |lambda| up to 1-1e-9; beyond that "no finite solution"
 
-__global__ void __launch_bounds__(128)
-k_dare(int64_t B, int method, int guard, double dt,
+B2C_HD void dare_solve_one(int64_t i, int64_t B, int method, int guard, double dt,
        double q0, double q1, double q2, double r0, double r1,
        const double* __restrict__ v, const double* __restrict__ th,
        double* __restrict__ Kout, double* __restrict__ Pout,
        int32_t* __restrict__ iters, int32_t* __restrict__ status) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= B) return;
     LinModel lm = b2c_linearize_point(b2c_guard_v(v[i], guard), th[i], dt, method);
     M3 A0 = {{lm.adiag, 0.0, lm.a13, 0.0, lm.adiag, lm.a23, 0.0, 0.0, lm.adiag}};
     // B (3x2): [[b11,b12],[b21,b22],[0,b32]]
@@ -207,7 +204,14 @@ k_dare(int64_t B, int method, int guard, double dt,
         m3_symmetrize(Gn);
         G = Gn;
         if (!(hmax < 1e300)) { st = B2C_NONFINITE; break; }   // catches NaN and overflow
-        if (dmax <= 1e-15 * hmax) { st = B2C_OK; ++it; break; }
+        if (dmax <= 1e-15 * hmax) {
+            // A_k = (closed loop)^(2^k) must have died out; if it has not, the pencil has an
+            // eigenvalue on the unit circle (e.g. v = 0: scipy raises LinAlgError there)
+            double amax = 0.0;
+#pragma unroll
+            for (int e = 0; e < 9; e++) amax = fmax(amax, fabs(A.m[e]));
+            st = (amax < 1e-3) ? B2C_OK : B2C_MAXITER; ++it; break;
+        }
     }
     // K = (R + B'PB)^-1 B'PA   (lqr_controller.py:130-132), P = H
     // PB (3x2)
@@ -252,6 +256,16 @@ k_dare(int64_t B, int method, int guard, double dt,
     if (status) status[i] = st;
 }
 
+__global__ void __launch_bounds__(128)
+k_dare(int64_t B, int method, int guard, double dt,
+       double q0, double q1, double q2, double r0, double r1,
+       const double* __restrict__ v, const double* __restrict__ th,
+       double* __restrict__ Kout, double* __restrict__ Pout,
+       int32_t* __restrict__ iters, int32_t* __restrict__ status) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B) dare_solve_one(i, B, method, guard, dt, q0, q1, q2, r0, r1, v, th, Kout, Pout, iters, status);
+}
+
 int b2c_dare_dev(b2c_ctx* ctx, int64_t B, int method, int guard, double dt,
                  const double Qd[3], const double Rd[2], const double* v, const double* th,
                  double* K, double* P, int32_t* iters, int32_t* status) {
@@ -294,3 +308,25 @@ int b2c_lqr_control_dev(b2c_ctx* ctx, int64_t B, double v_max, double w_max,
     B2C_CHECK_LAUNCH(ctx);
     return 0;
 }
+
+#ifdef B2C_HOST_EMUL
+// Test-only: the same per-instance code on the host (tests/ "not gpu" coverage of the kernel math).
+extern "C" int b2c_emul_dare(int64_t B, int method, int guard, double dt, const double Qd[3],
+                             const double Rd[2], const double* v, const double* th,
+                             double* K, double* P, int32_t* iters, int32_t* status) {
+    for (int64_t i = 0; i < B; ++i)
+        dare_solve_one(i, B, method, guard, dt, Qd[0], Qd[1], Qd[2], Rd[0], Rd[1], v, th, K, P, iters, status);
+    return 0;
+}
+extern "C" int b2c_emul_linearize(int64_t B, int method, int guard, double dt, const double* v,
+                                  const double* th, double* Ad, double* Bd) {
+    for (int64_t i = 0; i < B; ++i) {
+        LinModel m = b2c_linearize_point(b2c_guard_v(v[i], guard), th[i], dt, method);
+        double a[9] = {m.adiag, 0, m.a13, 0, m.adiag, m.a23, 0, 0, m.adiag};
+        double b[6] = {m.b11, m.b12, m.b21, m.b22, 0, m.b32};
+        for (int e = 0; e < 9; e++) Ad[e * B + i] = a[e];
+        for (int e = 0; e < 6; e++) Bd[e * B + i] = b[e];
+    }
+    return 0;
+}
+#endif

@@ -46,7 +46,7 @@ template <bool BS1> struct Lay {
 #define SC(f) a.scratch[(int64_t)(f) * a.B + i]
 
 // np.unwrap step (numpy/lib/function_base.py semantics, period 2pi, discont pi)
-__device__ __forceinline__ double unwrap_correction(double dd) {
+B2C_HD double unwrap_correction(double dd) {
     const double PI = 3.141592653589793, TWO_PI = 6.283185307179586;
     double m = fmod(dd + PI, TWO_PI);
     if (m < 0.0) m += TWO_PI;                 // python-style modulo
@@ -62,7 +62,7 @@ __device__ __forceinline__ double unwrap_correction(double dd) {
 // update  w+ = clip(w - alpha*kf - K (z+ - z))  (USE_GAIN=true, written to buffer `dst`), and
 // accumulates cost + the per-super-stage quadratic model at the NEW trajectory.
 template <bool BS1, bool USE_GAIN>
-__device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, double z0t,
+B2C_HD double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, double z0t,
                                               int src, int dst, double alpha, double& max_viol,
                                               bool& infeasible, double& lamx, double& lamy, double& lamt) {
     using L = Lay<BS1>;
@@ -80,8 +80,8 @@ __device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, doubl
         if (ltv) {
             lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
             for (int k = k_begin; k < k_end; ++k) {
-                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
-                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                double ur0 = B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i);
                 lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
                 lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
             }
@@ -108,25 +108,25 @@ __device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, doubl
         double gz[3] = {0, 0, 0}, gu[2] = {0, 0};
         for (int k = k_begin; k < k_end; ++k) {
             double ex = zx, ey = zy, et = zt, uo0 = 0.0, uo1 = 0.0;
-            const double prx = __ldg(a.xref + (int64_t)(3 * k) * a.B + i);
-            const double pry = __ldg(a.xref + (int64_t)(3 * k + 1) * a.B + i);
+            const double prx = B2C_LDG(a.xref + (int64_t)(3 * k) * a.B + i);
+            const double pry = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * a.B + i);
             if (ltv) {
-                uo0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
-                uo1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                uo0 = B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i);
+                uo1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i);
             } else {
-                ex -= prx; ey -= pry; et -= __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+                ex -= prx; ey -= pry; et -= B2C_LDG(a.xref + (int64_t)(3 * k + 2) * a.B + i);
             }
             double wxx = a.q0, wxy = 0.0, wyy = a.q1;
             double gx = a.q0 * ex, gy = a.q1 * ey, gt = a.q2 * et;
             J += a.q0 * ex * ex + a.q1 * ey * ey + a.q2 * et * et;
             for (int m = 0; m < M; ++m) {                      // soft obstacle rows, :439-468 / :238-270
-                const double obx = __ldg(a.obs + (int64_t)(3 * m) * a.B + i);
-                const double oby = __ldg(a.obs + (int64_t)(3 * m + 1) * a.B + i);
-                const double obr = __ldg(a.obs + (int64_t)(3 * m + 2) * a.B + i);
+                const double obx = B2C_LDG(a.obs + (int64_t)(3 * m) * a.B + i);
+                const double oby = B2C_LDG(a.obs + (int64_t)(3 * m + 1) * a.B + i);
+                const double obr = B2C_LDG(a.obs + (int64_t)(3 * m + 2) * a.B + i);
                 const double ddx = prx - obx, ddy = pry - oby;
                 const double d2 = ddx * ddx + ddy * ddy;
                 if (d2 > 1e-4) {                               // dist > 0.01
-                    const double inv = rsqrt(d2);
+                    const double inv = B2C_RSQRT(d2);
                     const double nx = ddx * inv, ny = ddy * inv;
                     // LTV: p = p_ref + dz  => n.(p - o) = dist + n.dz ;  LTI: p = z
                     double lhs = ltv ? (d2 * inv + nx * zx + ny * zy) : (nx * (zx - obx) + ny * (zy - oby));
@@ -192,9 +192,9 @@ __device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, doubl
     // terminal cost (mpc_controller.py:412 / :212-213)
     double ex = zx, ey = zy, et = zt;
     if (!ltv) {
-        ex -= __ldg(a.xref + (int64_t)(3 * N) * a.B + i);
-        ey -= __ldg(a.xref + (int64_t)(3 * N + 1) * a.B + i);
-        et -= __ldg(a.xref + (int64_t)(3 * N + 2) * a.B + i);
+        ex -= B2C_LDG(a.xref + (int64_t)(3 * N) * a.B + i);
+        ey -= B2C_LDG(a.xref + (int64_t)(3 * N + 1) * a.B + i);
+        et -= B2C_LDG(a.xref + (int64_t)(3 * N + 2) * a.B + i);
     }
     J += a.p0 * ex * ex + a.p1 * ey * ey + a.p2 * et * et;
     lamx = a.p0 * ex; lamy = a.p1 * ey; lamt = a.p2 * et;
@@ -204,7 +204,7 @@ __device__ __forceinline__ double mpc_forward(const MpcArgs& a, int64_t i, doubl
 // ----- backward pass --------------------------------------------------------------------------
 // Riccati sweep on the stored model.  Returns the Newton decrement 1/2 sum qu' Quu^-1 qu.
 template <bool BS1>
-__device__ __forceinline__ double mpc_backward(const MpcArgs& a, int64_t i, int cur,
+B2C_HD double mpc_backward(const MpcArgs& a, int64_t i, int cur,
                                                double lamx, double lamy, double lamt) {
     using L = Lay<BS1>;
     const int N = a.N, Nb = a.Nb;
@@ -249,8 +249,8 @@ __device__ __forceinline__ double mpc_backward(const MpcArgs& a, int64_t i, int 
             const int k_begin = j * a.bs, k_end = (j == Nb - 1) ? N : (k_begin + a.bs);
             lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
             for (int k = k_begin; k < k_end; ++k) {
-                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
-                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                double ur0 = B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i);
                 lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
                 lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
             }
@@ -316,27 +316,24 @@ __device__ __forceinline__ double mpc_backward(const MpcArgs& a, int64_t i, int 
 #define MPC_LS_MAX 14
 
 template <bool BS1>
-__global__ void __launch_bounds__(MPC_TPB)
-k_mpc(const MpcArgs a) {
+B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
     using L = Lay<BS1>;
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.B) return;
     const int N = a.N, Nb = a.Nb;
     const bool ltv = (a.kind == B2C_MPC_LTV);
 
     // ---- setup: linearize along the reference (K1 fused), initial state, initial inputs -------
-    const double x0x = __ldg(a.x0 + i), x0y = __ldg(a.x0 + a.B + i), x0t = __ldg(a.x0 + 2 * a.B + i);
-    const double r0x = __ldg(a.xref + i), r0y = __ldg(a.xref + a.B + i), r0t = __ldg(a.xref + 2 * a.B + i);
+    const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + a.B + i), x0t = B2C_LDG(a.x0 + 2 * a.B + i);
+    const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + a.B + i), r0t = B2C_LDG(a.xref + 2 * a.B + i);
     double z0x, z0y, z0t;
     if (ltv) {                                    // mpc_controller.py:392-401, :421
         z0x = x0x - r0x; z0y = x0y - r0y; z0t = b2c_wrap(x0t - r0t);
         double th_prev = r0t, cum = 0.0;          // np.unwrap along the horizon
         for (int k = 0; k < N; ++k) {
-            const double th_raw = __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+            const double th_raw = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * a.B + i);
             if (k > 0) cum += unwrap_correction(th_raw - th_prev);
             th_prev = th_raw;
             const double th = th_raw + cum;
-            const double vr = b2c_guard_v(__ldg(a.uref + (int64_t)(2 * k) * a.B + i), B2C_GUARD_MPC);   // :425
+            const double vr = b2c_guard_v(B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i), B2C_GUARD_MPC);   // :425
             double s, c; sincos(th, &s, &c);
             SC(L::ab(k) + 0) = -vr * s * a.dt; SC(L::ab(k) + 1) = vr * c * a.dt;
             SC(L::ab(k) + 2) = c * a.dt;       SC(L::ab(k) + 3) = s * a.dt;
@@ -344,13 +341,13 @@ k_mpc(const MpcArgs a) {
         for (int j = 0; j < Nb; ++j) { SC(L::w(N, Nb, 0, j)) = 0.0; SC(L::w(N, Nb, 0, j) + 1) = 0.0; }
     } else {                                      // :186-190, :223
         z0x = x0x; z0y = x0y; z0t = x0t;
-        const double vr = b2c_guard_v(__ldg(a.uref + i), B2C_GUARD_MPC);
+        const double vr = b2c_guard_v(B2C_LDG(a.uref + i), B2C_GUARD_MPC);
         double s, c; sincos(r0t, &s, &c);
         for (int k = 0; k < N; ++k) {
             SC(L::ab(k) + 0) = -vr * s * a.dt; SC(L::ab(k) + 1) = vr * c * a.dt;
             SC(L::ab(k) + 2) = c * a.dt;       SC(L::ab(k) + 3) = s * a.dt;
-            SC(L::w(N, Nb, 0, k)) = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
-            SC(L::w(N, Nb, 0, k) + 1) = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+            SC(L::w(N, Nb, 0, k)) = B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i);
+            SC(L::w(N, Nb, 0, k) + 1) = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i);
         }
     }
     // clip the initial inputs into their boxes (bounds recomputed exactly as in the passes)
@@ -361,8 +358,8 @@ k_mpc(const MpcArgs a) {
             const int k_begin = j * a.bs, k_end = (j == Nb - 1) ? N : (k_begin + a.bs);
             lb0 = -1e300; ub0 = 1e300; lb1 = -1e300; ub1 = 1e300;
             for (int k = k_begin; k < k_end; ++k) {
-                double ur0 = __ldg(a.uref + (int64_t)(2 * k) * a.B + i);
-                double ur1 = __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i);
+                double ur0 = B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i);
+                double ur1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i);
                 lb0 = fmax(lb0, -a.v_max - ur0); ub0 = fmin(ub0, a.v_max - ur0);
                 lb1 = fmax(lb1, -a.w_max - ur1); ub1 = fmin(ub1, a.w_max - ur1);
             }
@@ -405,7 +402,7 @@ k_mpc(const MpcArgs a) {
     }
 
     // ---- outputs ---------------------------------------------------------------------------------
-    const double ur00 = __ldg(a.uref + i), ur01 = __ldg(a.uref + a.B + i);
+    const double ur00 = B2C_LDG(a.uref + i), ur01 = B2C_LDG(a.uref + a.B + i);
     double u00, u01, Jout;
     int sc = a.step_count ? a.step_count[i] : a.ramp_up_steps;
     if (st == B2C_OK) {
@@ -419,9 +416,9 @@ k_mpc(const MpcArgs a) {
                 if (a.xpred) {
                     double ax = zx, ay = zy, at = zt;
                     if (ltv) {
-                        ax += __ldg(a.xref + (int64_t)(3 * k) * a.B + i);
-                        ay += __ldg(a.xref + (int64_t)(3 * k + 1) * a.B + i);
-                        at += __ldg(a.xref + (int64_t)(3 * k + 2) * a.B + i);
+                        ax += B2C_LDG(a.xref + (int64_t)(3 * k) * a.B + i);
+                        ay += B2C_LDG(a.xref + (int64_t)(3 * k + 1) * a.B + i);
+                        at += B2C_LDG(a.xref + (int64_t)(3 * k + 2) * a.B + i);
                     }
                     a.xpred[(int64_t)(3 * k) * a.B + i] = ax;
                     a.xpred[(int64_t)(3 * k + 1) * a.B + i] = ay;
@@ -431,8 +428,8 @@ k_mpc(const MpcArgs a) {
                 int j = k / a.bs; if (j > Nb - 1) j = Nb - 1;
                 const double wk0 = SC(L::w(N, Nb, cur, j)), wk1 = SC(L::w(N, Nb, cur, j) + 1);
                 if (a.useq) {
-                    a.useq[(int64_t)(2 * k) * a.B + i] = ltv ? (wk0 + __ldg(a.uref + (int64_t)(2 * k) * a.B + i)) : wk0;
-                    a.useq[(int64_t)(2 * k + 1) * a.B + i] = ltv ? (wk1 + __ldg(a.uref + (int64_t)(2 * k + 1) * a.B + i)) : wk1;
+                    a.useq[(int64_t)(2 * k) * a.B + i] = ltv ? (wk0 + B2C_LDG(a.uref + (int64_t)(2 * k) * a.B + i)) : wk0;
+                    a.useq[(int64_t)(2 * k + 1) * a.B + i] = ltv ? (wk1 + B2C_LDG(a.uref + (int64_t)(2 * k + 1) * a.B + i)) : wk1;
                 }
                 const double a_k = SC(L::ab(k)), b_k = SC(L::ab(k) + 1), c_k = SC(L::ab(k) + 2), s_k = SC(L::ab(k) + 3);
                 const double nzx = zx + a_k * zt + c_k * wk0, nzy = zy + b_k * zt + s_k * wk0;
@@ -451,7 +448,7 @@ k_mpc(const MpcArgs a) {
         const double e0 = x0x - r0x, e2 = b2c_wrap(x0t - r0t);
         u00 = b2c_clip(ur00 + (-1.0 * e0), -a.v_max, a.v_max);
         u01 = b2c_clip(ur01 + (-0.5 * e2), -a.w_max, a.w_max);
-        Jout = __longlong_as_double(0x7ff0000000000000LL);   // +inf
+        Jout = (double)INFINITY;   // +inf
         max_viol = 0.0;
         for (int k = 0; k <= N; ++k) {
             if (a.xpred) {
@@ -470,6 +467,13 @@ k_mpc(const MpcArgs a) {
     if (a.status) a.status[i] = st;
     if (a.iters) a.iters[i] = it;
     if (a.slack_used) a.slack_used[i] = (max_viol > 1e-6) ? 1 : 0;   // :485 / :294-296
+}
+
+template <bool BS1>
+__global__ void __launch_bounds__(MPC_TPB)
+k_mpc(const MpcArgs a) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.B) mpc_solve_one<BS1>(a, i);
 }
 
 }  // namespace
@@ -521,3 +525,32 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     B2C_CHECK_LAUNCH(ctx);
     return 0;
 }
+
+#ifdef B2C_HOST_EMUL
+#include <vector>
+// Test-only: the same per-instance solver on the host, SoA host pointers (see b2c_mpc_dev).
+extern "C" int b2c_emul_mpc(int64_t B, const b2c_mpc_params* p,
+                            const double* x0, const double* xref, const double* uref, const double* obs,
+                            int32_t* step_count, double* u0, double* cost, int32_t* status,
+                            int32_t* iters, int32_t* slack_used, double* useq, double* xpred) {
+    MpcArgs a;
+    a.B = B; a.kind = p->kind; a.N = p->N; a.M = p->M;
+    a.bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
+    a.Nb = (a.N + a.bs - 1) / a.bs;
+    a.max_iter = p->max_iter > 0 ? p->max_iter : 60;
+    a.ramp_up_steps = p->ramp_up_steps; a.soft = p->soft;
+    a.q0 = p->Qd[0]; a.q1 = p->Qd[1]; a.q2 = p->Qd[2]; a.r0 = p->Rd[0]; a.r1 = p->Rd[1];
+    a.p0 = p->Pd[0]; a.p1 = p->Pd[1]; a.p2 = p->Pd[2];
+    a.d_safe = p->d_safe; a.rho = p->rho; a.v_max = p->v_max; a.w_max = p->w_max; a.dt = p->dt;
+    a.tol = p->tol > 0 ? p->tol : 1e-14;
+    a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
+    a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
+    a.useq = useq; a.xpred = xpred;
+    std::vector<double> scratch((size_t)mpc_fields(p) * (size_t)B);
+    a.scratch = scratch.data();
+    for (int64_t i = 0; i < B; ++i) {
+        if (a.bs == 1) mpc_solve_one<true>(a, i); else mpc_solve_one<false>(a, i);
+    }
+    return 0;
+}
+#endif

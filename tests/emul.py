@@ -1,0 +1,75 @@
+"""Test-only: run the per-instance kernel code (mpc_solve_one / dare_solve_one, compiled for the host
+with -DB2C_HOST_EMUL into tests/_emul/libb2c_emul.so) on the CPU.  Not part of the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "risk-aware-hybrid-lqr-mpc-navigation-for-autonomous-systems_b200", "csrc")
+SO = os.path.join(ROOT, "tests", "_emul", "libb2c_emul.so")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        srcs = [os.path.join(CSRC, f) for f in ("mpc.cu", "lin_dare.cu", "api.cu", "b2c_common.cuh")]
+        if not os.path.exists(SO) or any(os.path.getmtime(s) > os.path.getmtime(SO) for s in srcs):
+            subprocess.check_call(["make", "-C", CSRC, "emul"], stdout=subprocess.DEVNULL)
+        _lib = C.CDLL(SO)
+    return _lib
+
+
+def _soa(a, B):
+    return np.ascontiguousarray(np.asarray(a, float).reshape(B, -1).T)
+
+
+def mpc(params, x0, xref, uref, obs, step_count=None):
+    from hybrid_controller import _native as nat
+    N, M = params.N, params.M
+    x0 = np.asarray(x0, float).reshape(-1, 3)
+    B = x0.shape[0]
+    sx0, sxr, sur = _soa(x0, B), _soa(xref, B), _soa(uref, B)
+    sob = _soa(obs, B) if M else np.zeros((1, B))
+    sc = None if step_count is None else np.ascontiguousarray(step_count, np.int32).copy()
+    u0, cost = np.empty((2, B)), np.empty(B)
+    st, it, sl = (np.empty(B, np.int32) for _ in range(3))
+    useq, xpred = np.empty((2 * N, B)), np.empty((3 * (N + 1), B))
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    f = lib().b2c_emul_mpc
+    f.argtypes = [C.c_int64, C.POINTER(nat.MpcParams)] + [C.c_void_p] * 12
+    rc = f(B, C.byref(params), p(sx0), p(sxr), p(sur), p(sob), p(sc), p(u0), p(cost), p(st), p(it),
+           p(sl), p(useq), p(xpred))
+    assert rc == 0
+    return dict(u0=u0.T.copy(), cost=cost, status=st, iters=it, slack_used=sl,
+                useq=useq.T.reshape(B, N, 2).copy(), xpred=xpred.T.reshape(B, N + 1, 3).copy(),
+                step_count=sc)
+
+
+def dare(v, th, dt, Qd, Rd, method=1, guard=1):
+    v, th = np.ascontiguousarray(v, float).ravel(), np.ascontiguousarray(th, float).ravel()
+    B = v.size
+    K, P = np.empty((6, B)), np.empty((6, B))
+    it, st = np.empty(B, np.int32), np.empty(B, np.int32)
+    f = lib().b2c_emul_dare
+    f.argtypes = [C.c_int64, C.c_int, C.c_int, C.c_double, C.c_double * 3, C.c_double * 2] + [C.c_void_p] * 6
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    f(B, method, guard, dt, (C.c_double * 3)(*map(float, Qd)), (C.c_double * 2)(*map(float, Rd)),
+      p(v), p(th), p(K), p(P), p(it), p(st))
+    Pf = np.empty((B, 3, 3))
+    for (r, c), e in zip(((0, 0), (0, 1), (0, 2), (1, 1), (1, 2), (2, 2)), range(6)):
+        Pf[:, r, c] = P[e]; Pf[:, c, r] = P[e]
+    return K.T.reshape(B, 2, 3).copy(), Pf, it, st
+
+
+def linearize(v, th, dt, method=1, guard=0):
+    v, th = np.ascontiguousarray(v, float).ravel(), np.ascontiguousarray(th, float).ravel()
+    B = v.size
+    A, Bd = np.empty((9, B)), np.empty((6, B))
+    f = lib().b2c_emul_linearize
+    f.argtypes = [C.c_int64, C.c_int, C.c_int, C.c_double] + [C.c_void_p] * 4
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    f(B, method, guard, dt, p(v), p(th), p(A), p(Bd))
+    return A.T.reshape(B, 3, 3).copy(), Bd.T.reshape(B, 3, 2).copy()

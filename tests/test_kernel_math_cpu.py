@@ -1,0 +1,132 @@
+"""CPU: (1) libb2c.so loads and exports every symbol include/b2c.h declares (no compute call);
+(2) the per-instance kernel code (mpc_solve_one / dare_solve_one / b2c_linearize_point), compiled
+for the host into a TEST-ONLY library (tests/emul.py), agrees with the oracle -- so the kernel
+arithmetic is covered without a GPU; the -m gpu tests then check the real device path."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import emul
+from conftest import MPC_PRM6, MPC_PRM20, DEFAULT_OBS, ROOT
+from oracle import lin_dare, mpc_qp
+
+
+def test_abi_library_exports_every_declared_symbol():
+    from hybrid_controller import _native as nat
+    lib = nat.load_library()
+    hdr = open(os.path.join(ROOT, "include", "b2c.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(b2c_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in b2c.h but not exported"
+    assert declared == set(nat.SIGNATURES), declared ^ set(nat.SIGNATURES)
+    assert lib.b2c_version() == 100
+
+
+def test_product_has_no_host_emulation_path():
+    import subprocess
+    from hybrid_controller import _native as nat
+    syms = subprocess.run(["nm", "-D", nat.LIB_PATH], capture_output=True, text=True).stdout
+    assert "b2c_emul" not in syms
+
+
+def test_no_gpu_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from hybrid_controller import _native as nat
+    from hybrid_controller.controllers import LQRController
+    with pytest.raises(nat.B2CUnavailable):
+        LQRController().compute_gain(1.0, 0.0)
+
+
+def test_emul_linearize_and_dare_vs_reference_golden(golden):
+    r = golden["ref_py"]
+    for meth, key in ((1, "euler"), (2, "exact"), (0, "jac")):
+        A, B = emul.linearize(r["v"], r["th"], 0.02, method=meth)
+        assert np.abs(A - r[key + "_A"]).max() <= 4e-16 and np.abs(B - r[key + "_B"]).max() <= 4e-16
+    for tag in ("sim", "def", "aniso"):
+        K, P, it, st = emul.dare(r["v"], r["th"], 0.02, r[f"Qd_{tag}"], r[f"Rd_{tag}"])
+        assert (st == 0).all() and it.max() <= 30
+        relK = np.abs(K - r[f"K_{tag}"]).max(axis=(1, 2)) / np.abs(r[f"K_{tag}"]).max(axis=(1, 2))
+        relP = np.abs(P - r[f"P_{tag}"]).max(axis=(1, 2)) / np.abs(r[f"P_{tag}"]).max(axis=(1, 2))
+        assert relK.max() <= 1e-9 and relP.max() <= 1e-9
+    # no guard + v = 0: no stabilizing solution -> non-zero status and the reference's fallback gain
+    K, _, _, st = emul.dare([0.0], [0.3], 0.02, [15, 15, 8], [.1, .1], guard=0)
+    assert st[0] != 0 and np.array_equal(K[0], [[1, 0, 0], [0, 0, 1]])
+
+
+def _params(N, M, bs, kind=0, **kw):
+    from hybrid_controller import _native as nat
+    d = dict(Qd=[15, 15, 50], Rd=[.1, .1], Pd=[30, 30, 40], d_safe=.3, rho=5000., v_max=2., w_max=3., dt=.02)
+    d.update(kw)
+    return nat.mpc_params(kind, N, M, bs, d["Qd"], d["Rd"], d["Pd"], d["d_safe"], d["rho"], d["v_max"],
+                          d["w_max"], d["dt"])
+
+
+@pytest.mark.parametrize("N,bs,M", [(20, 1, 5), (6, 2, 3), (20, 3, 5), (7, 4, 1), (10, 1, 0), (1, 1, 2)])
+def test_emul_mpc_vs_oracle(N, bs, M):
+    from hybrid_controller import workloads as wl
+    B = 64
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=N * 10 + bs, obstacles=wl.DENSE_OBSTACLES[:M],
+                                          pos_jitter=0.2, th_jitter=0.5)
+    out = emul.mpc(_params(N, M, bs), x0, xr, ur, ob)
+    prm = dict(MPC_PRM20, N=N, block_size=bs)
+    assert (out["status"] == 0).all()
+    for b in range(B):
+        o = mpc_qp.solve_with_ltv(x0[b], xr[b], ur[b], ob[b], **prm)
+        assert np.abs(out["u0"][b] - o["optimal_control"]).max() <= 1e-4
+        assert abs(out["cost"][b] - o["cost"]) <= 1e-6 * abs(o["cost"])
+        assert bool(out["slack_used"][b]) == o["slack_used"]
+        assert np.abs(out["useq"][b] - o["control_sequence"]).max() <= 1e-4
+        assert np.abs(out["xpred"][b] - o["predicted_states"]).max() <= 1e-5
+
+
+def test_emul_mpc_g_mpc_golden(golden):
+    g = golden["g_mpc"]
+    traj = lin_dare.figure8(20.0)
+    ks = np.arange(0, 999, 5)
+    x0 = g["states"][ks]
+    xr = np.stack([lin_dare.segment(traj, k, 7)[0] for k in ks])
+    ur = np.stack([lin_dare.segment(traj, k, 7)[1][:6] for k in ks])
+    ob = np.broadcast_to(np.array(DEFAULT_OBS)[None], (len(ks), 3, 3))
+    out = emul.mpc(_params(6, 3, 2), x0, xr, ur, ob, step_count=np.arange(len(ks), dtype=np.int32))
+    assert (out["status"] == 0).all()
+    slack_ticks = set(g["slack_ticks"].tolist())
+    err = np.abs(out["u0"] - g["controls"][ks]).max(axis=1)
+    for k, e in zip(ks, err):
+        assert e < (2e-3 if k in slack_ticks else 5e-6), (k, e)
+    assert sorted(ks[out["slack_used"] == 1].tolist()) == sorted(slack_ticks)
+
+
+def test_emul_mpc_lti_and_fallback():
+    from hybrid_controller import workloads as wl
+    table = wl.figure8_table()
+    rng = np.random.default_rng(5)
+    prm = dict(N=10, Qd=[10, 10, 1], Rd=[.1, .1], Pd=[20, 20, 2], d_safe=.3, rho=1000., v_max=1., w_max=1.5, dt=.02)
+    for k0 in (0, 45, 120, 400, 985):
+        idx = np.minimum(k0 + np.arange(11), len(table) - 1)
+        xr, ur = table[idx, 1:4], table[idx, 4:6][:10]
+        x0 = xr[0] + rng.uniform(-.1, .1, 3)
+        out = emul.mpc(_params(10, 3, 1, kind=1, **{k: v for k, v in prm.items() if k != 'N'}), x0[None], xr[None], ur[None], np.array(DEFAULT_OBS)[None])
+        o = mpc_qp.solve(x0, xr, ur, DEFAULT_OBS, **prm)
+        assert out["status"][0] == 0
+        assert np.abs(out["u0"][0] - o["optimal_control"]).max() <= 1e-4
+        assert abs(out["cost"][0] - o["cost"]) <= 1e-6 * abs(o["cost"])
+        assert np.abs(out["xpred"][0] - o["predicted_states"]).max() <= 1e-5
+    xb = x0.copy(); xb[1] = np.nan
+    out = emul.mpc(_params(10, 3, 1, kind=1, **{k: v for k, v in prm.items() if k != 'N'}), xb[None], xr[None], ur[None], np.array(DEFAULT_OBS)[None])
+    assert out["status"][0] != 0 and np.isinf(out["cost"][0])
+
+
+def test_emul_mpc_infeasible_blocked_bounds():
+    """block of 2 whose reference inputs differ by more than the box width -> no feasible du."""
+    xr = np.zeros((5, 3)); ur = np.array([[1.9, 0.0], [-1.9, 0.0], [0.5, 0], [0.5, 0]])
+    p = _params(4, 0, 2, v_max=1.0)
+    out = emul.mpc(p, np.zeros((1, 3)), xr[None], ur[None], np.zeros((1, 0, 3)))
+    assert out["status"][0] == 3 and np.isinf(out["cost"][0])
+    fb = mpc_qp.fallback(np.zeros(3), xr, ur, 4, 1.0, 3.0)
+    assert np.allclose(out["u0"][0], fb["optimal_control"])
