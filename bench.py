@@ -147,7 +147,8 @@ def run_gpu(args):
     B, N, M = B_PER_GPU, HORIZON, N_OBS
     K, W = args.steps, max(args.warmup, 3)
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)          # kernels, copies and timing events all on this stream
+    torch.cuda.set_stream(stream)
     ctx = nat.Context(local, stream=stream.cuda_stream)
     prm = nat.mpc_params(nat.MPC_LTV, N, M, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02)
 

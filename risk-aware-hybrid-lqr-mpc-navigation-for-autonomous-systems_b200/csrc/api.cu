@@ -47,17 +47,20 @@ int b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream) {
     cudaDeviceProp prop;
     B2C_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
-    if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
-    else {
-        e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-        if (e != cudaSuccess) { delete c; return b2c_cuda_fail(e, "stream create", __FILE__, __LINE__); }
-        c->own_stream = true;
-    }
+    // the caller's stream is used as given -- a null handle is the legacy default stream
+    c->stream = (cudaStream_t)cuda_stream; c->own_stream = false;
     *out = c;
     return 0;
 }
 
-int b2c_create(b2c_ctx** out, int device) { return b2c_create_on_stream(out, device, nullptr); }
+int b2c_create(b2c_ctx** out, int device) {
+    int rc = b2c_create_on_stream(out, device, nullptr);
+    if (rc) return rc;
+    cudaError_t e = cudaStreamCreateWithFlags(&(*out)->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete *out; *out = nullptr; return b2c_cuda_fail(e, "stream create", __FILE__, __LINE__); }
+    (*out)->own_stream = true;
+    return 0;
+}
 
 void b2c_destroy(b2c_ctx* c) {
     if (!c) return;

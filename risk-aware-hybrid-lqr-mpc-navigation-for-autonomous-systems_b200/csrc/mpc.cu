@@ -311,9 +311,43 @@ B2C_HD double mpc_backward(const MpcArgs& a, int64_t i, int cur,
     return dec;
 }
 
+// ----- globalisation fallback -------------------------------------------------------------------
+// Clipped closed-loop roll-outs are the fast path but carry no descent guarantee when many inputs
+// saturate.  If they fail, the gains are rewritten in place as the OPEN-LOOP Newton direction of the
+// linear model (d_j = -kf_j - K_j dz_j, dz_{j+1} = Abar dz_j + Bbar d_j), after which the forward pass
+// evaluates the projection arc P[w + alpha d] -- Bertsekas' projected Newton method, for which a
+// small enough alpha always decreases the cost because the frozen inputs are decoupled in Quu.
+template <bool BS1>
+B2C_HD void mpc_gains_to_open_loop(const MpcArgs& a, int64_t i) {
+    using L = Lay<BS1>;
+    const int N = a.N, Nb = a.Nb;
+    double dx = 0.0, dy = 0.0, dth = 0.0;
+    for (int j = 0; j < Nb; ++j) {
+        const int g = L::gain(N, Nb, j);
+        const double d0 = -SC(g + 6) - (SC(g + 0) * dx + SC(g + 1) * dy + SC(g + 2) * dth);
+        const double d1 = -SC(g + 7) - (SC(g + 3) * dx + SC(g + 4) * dy + SC(g + 5) * dth);
+        double al, be, g00, g01, g10, g11, g21;
+        if (BS1) {
+            al = SC(L::ab(j)); be = SC(L::ab(j) + 1); g00 = SC(L::ab(j) + 2); g10 = SC(L::ab(j) + 3);
+            g01 = 0.0; g11 = 0.0; g21 = a.dt;
+        } else {
+            const int mo = L::model(N, Nb, j);
+            al = SC(mo + 20); be = SC(mo + 21);
+            g00 = SC(mo + 22); g01 = SC(mo + 23); g10 = SC(mo + 24); g11 = SC(mo + 25); g21 = SC(mo + 26);
+        }
+        const double ndx = dx + al * dth + g00 * d0 + g01 * d1;
+        const double ndy = dy + be * dth + g10 * d0 + g11 * d1;
+        dth = dth + g21 * d1; dx = ndx; dy = ndy;
+#pragma unroll
+        for (int e = 0; e < 6; e++) SC(g + e) = 0.0;
+        SC(g + 6) = -d0; SC(g + 7) = -d1;
+    }
+}
+
 // ----- the solver kernel -----------------------------------------------------------------------
 #define MPC_TPB 128
-#define MPC_LS_MAX 14
+#define MPC_LS_CLOSED 3    // closed-loop trials (alpha = 1, 1/2, 1/4) before the projection arc
+#define MPC_LS_MAX 18
 
 template <bool BS1>
 B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
@@ -394,7 +428,9 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
             J = Jn; cur ^= 1; lamx = tlx; lamy = tly; lamt = tlt; max_viol = tviol; need_backward = true;
         } else {
             alpha *= 0.5;
-            if (++ls >= MPC_LS_MAX) {             // cannot decrease any further: rounding floor or stall
+            ++ls;
+            if (ls == MPC_LS_CLOSED) { mpc_gains_to_open_loop<BS1>(a, i); alpha = 1.0; }
+            if (ls >= MPC_LS_MAX) {               // cannot decrease any further: rounding floor or stall
                 st = (dec <= 1e-9 * fmax(1.0, fabs(J))) ? B2C_OK : B2C_MAXITER;
                 break;
             }

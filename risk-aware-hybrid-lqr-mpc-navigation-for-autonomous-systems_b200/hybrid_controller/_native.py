@@ -99,7 +99,9 @@ class Context:
     def __init__(self, device=-1, stream=None):
         self.lib = load_library()
         h = _P()
-        rc = (self.lib.b2c_create_on_stream(C.byref(h), int(device), _P(stream)) if stream
+        # stream=None: the context creates its own non-blocking stream; an int (0 = default stream,
+        # or e.g. torch.cuda.current_stream().cuda_stream) is used as given
+        rc = (self.lib.b2c_create_on_stream(C.byref(h), int(device), _P(int(stream))) if stream is not None
               else self.lib.b2c_create(C.byref(h), int(device)))
         if rc != 0:
             raise B2CUnavailable(self.lib.b2c_last_error().decode())

@@ -97,11 +97,24 @@ def solve(p, max_iter=50, verbose=False):
             return w, J, it, True
         alpha = 1.0
         ok = False
-        while alpha > 1e-4:
+        ntry = 0
+        open_loop = False
+        while ntry < 3 + 14:
+            if ntry == 3 and not open_loop:
+                # closed-loop clipped roll-outs failed: switch to the projection arc P[w + alpha d]
+                # with d the Newton direction of the LINEAR model (Bertsekas 1982: guaranteed descent)
+                dz = np.zeros(3); d = np.zeros_like(w)
+                for j in range(Nb):
+                    d[j] = -kf[j] - K[j] @ dz
+                    dz = st[j][5] @ dz + st[j][6] @ d[j]
+                open_loop = True; alpha = 1.0
             wn = np.zeros_like(w)
             z = p["z0"].copy(); zn = p["z0"].copy()
             for j in range(Nb):
-                wn[j] = np.clip(w[j] - alpha * kf[j] - K[j] @ (zn - z), p["lb"][j], p["ub"][j])
+                if open_loop:
+                    wn[j] = np.clip(w[j] + alpha * d[j], p["lb"][j], p["ub"][j])
+                else:
+                    wn[j] = np.clip(w[j] - alpha * kf[j] - K[j] @ (zn - z), p["lb"][j], p["ub"][j])
                 for k in range(j * p["bs"], min((j + 1) * p["bs"], p["N"])):
                     z = p["A"][k] @ z + p["B"][k] @ w[j]
                     zn = p["A"][k] @ zn + p["B"][k] @ wn[j]
@@ -110,6 +123,7 @@ def solve(p, max_iter=50, verbose=False):
                 ok = True
                 break
             alpha *= 0.5
+            ntry += 1
         if not ok:
             return w, J, it, False
         w, J, st, lamN = wn, Jn, stn, lamNn
