@@ -42,10 +42,12 @@ def _oracle_solve(args):
     return o["optimal_control"]
 
 
-def cpu_arm(n_instances, seed, pool):
-    """Time the CPU implementation of the path on `n_instances` config-4 instances (all host cores)."""
+def cpu_arm(n_instances, seed, pool, global_batch=None):
+    """Time the CPU implementation of the path on `n_instances` config-4 instances (all host cores).
+    With `global_batch` the instances are the FIRST n of that seeded global batch (same as the GPU's)."""
     from hybrid_controller import workloads as wl
-    x0, xr, ur, ob = wl.config4_instances(n_instances, N=HORIZON, seed=seed)
+    x0, xr, ur, ob = wl.config4_instances(global_batch or n_instances, N=HORIZON, seed=seed, start=0,
+                                          count=n_instances)
     items = [(x0[i], xr[i], ur[i], ob[i]) for i in range(n_instances)]
     t0 = time.perf_counter()
     res = pool.map(_oracle_solve, items, chunksize=max(1, n_instances // (4 * pool._processes)))
@@ -266,7 +268,7 @@ def run_gpu(args):
         pool, cores = make_pool()
         cpu_arm(max(cores, 16), 7, pool)
         n_s = max(128, 32 * cores)
-        v_cpu, dt_cpu, u_cpu = cpu_arm(n_s, 100, pool)          # same instances as dev_sets[0][:n_s]
+        v_cpu, dt_cpu, u_cpu = cpu_arm(n_s, 100, pool, global_batch=gB)   # = dev_sets[0][:n_s]
         pool.close()
         step_dev(0)
         torch.cuda.synchronize()
