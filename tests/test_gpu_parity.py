@@ -351,3 +351,43 @@ def test_mpc_full_size_properties(hc):
     assert np.array_equal(outs["u0"], out["u0"][s:s + c]) and np.array_equal(outs["cost"], out["cost"][s:s + c])
     # the no-obstacle, unsaturated subset is a pure LQ problem: 1 Newton step
     assert out["iters"].min() >= 1 and out["iters"].max() <= 30
+
+
+def test_mpc_config2_closed_loop_vs_g_mpc(hc, golden):
+    """Config 2: run_mpc_simulation's loop with the drop-in classes (batch = 1 latency path) vs G-MPC.
+    Tolerance as in the CPU twin: states 5e-4, controls 5e-3 (OSQP's own error band in the log)."""
+    import time
+    from hybrid_controller.controllers.mpc_controller import MPCController, Obstacle
+    from hybrid_controller.models.differential_drive import DifferentialDriveRobot
+    from hybrid_controller.trajectory.reference_generator import ReferenceTrajectoryGenerator
+    g = golden["g_mpc"]
+    robot = DifferentialDriveRobot(v_max=2.0, omega_max=3.0)
+    gen = ReferenceTrajectoryGenerator(A=2.0, a=0.5, dt=0.02)
+    gen.generate(20.0)
+    mpc = MPCController(horizon=6, Q_diag=[15.0, 15.0, 50.0], R_diag=[0.1, 0.1], P_diag=[30.0, 30.0, 40.0],
+                        d_safe=0.3, slack_penalty=5000.0, dt=0.02, v_max=2.0, omega_max=3.0, solver='OSQP',
+                        block_size=2)
+    obstacles = [Obstacle(x=1.0, y=0.5, radius=0.2), Obstacle(x=-0.5, y=-1.0, radius=0.25),
+                 Obstacle(x=1.5, y=-0.3, radius=0.15)]
+    x = gen.get_reference_at_index(0)[0].copy()
+    ex = eu = 0.0
+    slack, lat = [], []
+    for k in range(999):
+        x_refs, u_refs = gen.get_trajectory_segment(k, mpc.N + 1)
+        if k % 5 == 0:
+            t0 = time.perf_counter()
+            sol = mpc.solve_with_ltv(x, x_refs, u_refs, obstacles)
+            lat.append((time.perf_counter() - t0) * 1e3)
+            assert sol.status == "optimal"
+            if sol.slack_used:
+                slack.append(k)
+        u = sol.optimal_control
+        ex = max(ex, np.abs(x - g["states"][k]).max())
+        eu = max(eu, np.abs(u - g["controls"][k]).max())
+        x = robot.simulate_step(x, u, 0.02)
+    assert ex < 5e-4 and eu < 5e-3, (ex, eu)
+    assert slack == g["slack_ticks"].tolist()
+    lat = np.array(lat[5:])
+    print(f"\nbatch=1 solve_with_ltv latency: mean {lat.mean():.3f} ms  p50 {np.median(lat):.3f}  p99 "
+          f"{np.percentile(lat, 99):.3f} ms   (reference log: mean 82.6 ms, p99 154.5 ms)")
+    assert np.median(lat) < 5.0

@@ -130,3 +130,29 @@ def test_emul_mpc_infeasible_blocked_bounds():
     assert out["status"][0] == 3 and np.isinf(out["cost"][0])
     fb = mpc_qp.fallback(np.zeros(3), xr, ur, 4, 1.0, 3.0)
     assert np.allclose(out["u0"][0], fb["optimal_control"])
+
+
+def test_emul_mpc_closed_loop_vs_g_mpc(golden):
+    """Config 2 closed loop (run_mpc_simulation: solve every 5th tick, hold u, Euler plant) vs the
+    shipped log.  Stated tolerance: states 5e-4, controls 5e-3 -- the log's own OSQP eps=1e-5 error
+    (1.4e-3 on a slack-active control) re-enters the loop through the plant; slack ticks identical."""
+    g = golden["g_mpc"]
+    traj = lin_dare.figure8(20.0)
+    obs = np.array(DEFAULT_OBS)
+    prm = _params(6, 3, 2)
+    x = traj[0, 1:4].copy()
+    sc = np.zeros(1, np.int32)
+    ex = eu = 0.0
+    slack = []
+    for k in range(999):
+        if k % 5 == 0:
+            xr, ur = lin_dare.segment(traj, k, 7)
+            o = emul.mpc(prm, x[None], xr[None], ur[None, :6], obs[None], step_count=sc)
+            sc, u = o["step_count"], o["u0"][0]
+            if o["slack_used"][0]:
+                slack.append(k)
+        ex = max(ex, np.abs(x - g["states"][k]).max())
+        eu = max(eu, np.abs(u - g["controls"][k]).max())
+        x = lin_dare.plant_step(x, u, .02, 2., 3.)
+    assert ex < 5e-4 and eu < 5e-3, (ex, eu)
+    assert slack == g["slack_ticks"].tolist()
