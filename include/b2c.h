@@ -51,6 +51,8 @@ enum { B2C_GUARD_NONE = 0,    /* get_lqr_gain                lqr_controller.py:2
 /* per-instance status of the iterative kernels */
 enum { B2C_OK = 0, B2C_MAXITER = 1, B2C_NONFINITE = 2, B2C_INFEASIBLE = 3 };
 
+enum { B2C_MPC_ENGINE_AUTO = 0, B2C_MPC_ENGINE_GENERAL = 1, B2C_MPC_ENGINE_SLOTS = 2 };
+
 /* MPC problem kinds */
 enum { B2C_MPC_LTV = 0,       /* solve_with_ltv: error state, LTV, move blocking, theta unwrap */
        B2C_MPC_LTI = 1        /* solve: absolute state, one linearization, no unwrap           */ };
@@ -63,7 +65,8 @@ typedef struct {
     int32_t soft;             /* use_soft_constraints         (:152, :347)                      */
     int32_t max_iter;         /* Newton iteration cap (<=0: default 60)                         */
     int32_t ramp_up_steps;    /* cold-start ramp length       (:144), LTV only                  */
-    int32_t reserved;
+    int32_t engine;           /* kernel choice: 0 = automatic, 1 = general kernel (HBM scratch), 2 = persistent
+                                 slot kernel (shared-memory scratch; LTV, block_size 1, soft rows) or error -5 */
     double  Qd[3], Rd[2], Pd[3];
     double  d_safe, rho, v_max, w_max, dt;
     double  tol;              /* relative Newton-decrement tolerance (<=0: default 1e-14)       */

@@ -14,24 +14,9 @@
 // gradient are frozen) + a forward roll-out with feedback, clipping and a monotone line search.
 // When the active sets stop changing the step lands on the exact minimiser (to rounding), i.e. the
 // same point CVXPY/OSQP approximates to 1e-5; typical count is 1-8 iterations.
-#include "b2c_common.cuh"
+#include "mpc_args.cuh"
 
 namespace {
-
-struct MpcArgs {
-    int64_t B;
-    int kind, N, M, bs, Nb, max_iter, ramp_up_steps, soft;
-    double q0, q1, q2, r0, r1, p0, p1, p2;
-    double d_safe, rho, v_max, w_max, dt, tol;
-    const double* __restrict__ x0;
-    const double* __restrict__ xref;
-    const double* __restrict__ uref;
-    const double* __restrict__ obs;
-    int32_t* step_count;
-    double* u0; double* cost; int32_t* status; int32_t* iters; int32_t* slack_used;
-    double* useq; double* xpred;
-    double* scratch;
-};
 
 // scratch field map (each field is a length-B column; instance i lives at field*B + i)
 template <bool BS1> struct Lay {
@@ -44,18 +29,6 @@ template <bool BS1> struct Lay {
 };
 
 #define SC(f) a.scratch[(int64_t)(f) * a.B + i]
-
-// np.unwrap step (numpy/lib/function_base.py semantics, period 2pi, discont pi)
-B2C_HD double unwrap_correction(double dd) {
-    const double PI = 3.141592653589793, TWO_PI = 6.283185307179586;
-    double m = fmod(dd + PI, TWO_PI);
-    if (m < 0.0) m += TWO_PI;                 // python-style modulo
-    double ddmod = m - PI;
-    if (ddmod == -PI && dd > 0.0) ddmod = PI;
-    double corr = ddmod - dd;
-    if (fabs(dd) < PI) corr = 0.0;
-    return corr;
-}
 
 // ----- forward pass ---------------------------------------------------------------------------
 // Rolls the plant out from z0 under either the current inputs (USE_GAIN=false) or the Newton
@@ -346,8 +319,6 @@ B2C_HD void mpc_gains_to_open_loop(const MpcArgs& a, int64_t i) {
 
 // ----- the solver kernel -----------------------------------------------------------------------
 #define MPC_TPB 128
-#define MPC_LS_CLOSED 3    // closed-loop trials (alpha = 1, 1/2, 1/4) before the projection arc
-#define MPC_LS_MAX 18
 
 template <bool BS1>
 B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
@@ -522,6 +493,15 @@ static int mpc_fields(const b2c_mpc_params* p) {
 
 int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B) {
     if (!p || B <= 0) return 0;
+    MpcArgs a;
+    mpc_fill_args(a, B, p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                  nullptr, nullptr);
+    int tpb = 0;
+    if (p->engine != B2C_MPC_ENGINE_GENERAL && mpc_slots_eligible(a, &tpb)) {
+        // slot kernel: G[6N] + GG[8N] doubles per RESIDENT slot (one CTA per SM, 148 SMs assumed here)
+        int64_t slots = (B + tpb - 1) / tpb; if (slots > 148) slots = 148;
+        return (int64_t)14 * p->N * slots * tpb * (int64_t)sizeof(double) + 256;
+    }
     return (int64_t)mpc_fields(p) * B * (int64_t)sizeof(double);
 }
 
@@ -540,19 +520,15 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
     if (B <= 0) return 0;
     MpcArgs a;
-    a.B = B; a.kind = p->kind; a.N = p->N; a.M = p->M;
-    a.bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
-    a.Nb = (a.N + a.bs - 1) / a.bs;
-    a.max_iter = p->max_iter > 0 ? p->max_iter : 60;
-    a.ramp_up_steps = p->ramp_up_steps; a.soft = p->soft;
-    a.q0 = p->Qd[0]; a.q1 = p->Qd[1]; a.q2 = p->Qd[2]; a.r0 = p->Rd[0]; a.r1 = p->Rd[1];
-    a.p0 = p->Pd[0]; a.p1 = p->Pd[1]; a.p2 = p->Pd[2];
-    a.d_safe = p->d_safe; a.rho = p->rho; a.v_max = p->v_max; a.w_max = p->w_max; a.dt = p->dt;
-    a.tol = p->tol > 0 ? p->tol : 1e-14;
-    a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
-    a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
-    a.useq = useq; a.xpred = xpred;
-    const size_t need = (size_t)b2c_mpc_scratch_bytes(p, B);
+    mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
+    int tpb = 0;
+    const bool slots_ok = mpc_slots_eligible(a, &tpb);
+    if (p->engine == B2C_MPC_ENGINE_SLOTS && !slots_ok) {
+        b2c_set_error("slot kernel needs kind=LTV, block_size=1, soft rows and 10N+3M <= 907");
+        return -5;
+    }
+    if (slots_ok && p->engine != B2C_MPC_ENGINE_GENERAL) return mpc_slots_launch(ctx, a, tpb);
+    const size_t need = (size_t)mpc_fields(p) * (size_t)B * sizeof(double);
     int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, need, false);
     if (rc) return rc;
     a.scratch = (double*)ctx->scratch;
@@ -570,18 +546,7 @@ extern "C" int b2c_emul_mpc(int64_t B, const b2c_mpc_params* p,
                             int32_t* step_count, double* u0, double* cost, int32_t* status,
                             int32_t* iters, int32_t* slack_used, double* useq, double* xpred) {
     MpcArgs a;
-    a.B = B; a.kind = p->kind; a.N = p->N; a.M = p->M;
-    a.bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
-    a.Nb = (a.N + a.bs - 1) / a.bs;
-    a.max_iter = p->max_iter > 0 ? p->max_iter : 60;
-    a.ramp_up_steps = p->ramp_up_steps; a.soft = p->soft;
-    a.q0 = p->Qd[0]; a.q1 = p->Qd[1]; a.q2 = p->Qd[2]; a.r0 = p->Rd[0]; a.r1 = p->Rd[1];
-    a.p0 = p->Pd[0]; a.p1 = p->Pd[1]; a.p2 = p->Pd[2];
-    a.d_safe = p->d_safe; a.rho = p->rho; a.v_max = p->v_max; a.w_max = p->w_max; a.dt = p->dt;
-    a.tol = p->tol > 0 ? p->tol : 1e-14;
-    a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
-    a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
-    a.useq = useq; a.xpred = xpred;
+    mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
     std::vector<double> scratch((size_t)mpc_fields(p) * (size_t)B);
     a.scratch = scratch.data();
     for (int64_t i = 0; i < B; ++i) {

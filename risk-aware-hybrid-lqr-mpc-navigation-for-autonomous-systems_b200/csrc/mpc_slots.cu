@@ -1,0 +1,445 @@
+// K3 (fast path): persistent "slot" kernel for solve_with_ltv-shaped batches with block_size == 1
+// (HC/controllers/mpc_controller.py:345-522).  Same method as mpc.cu (slack elimination + projected
+// semismooth Newton with a Riccati inner solve), different machine mapping:
+//
+//   * one CTA per SM, one lane = one SLOT; a slot owns a private strip of SHARED memory holding the
+//     per-stage data of the instance it is working on:
+//        W[2N]  current inputs            U[8N]  union { Riccati gains K(6) k(2) | stage model(6) + previous inputs(2) }
+//        OB[3M] the instance's obstacles                         (10N + 3M doubles; 1,720 B at N=20, M=5)
+//     laid out [field][lane], i.e. bank-conflict free.  Forward and backward sweeps never touch HBM for
+//     the sequential part of the recursion.
+//   * read-only per-stage constants (cos*dt, sin*dt, u_ref, p_ref) are written once per instance into a
+//     slot-indexed global strip G[6N][nslots] (coalesced, L2-resident: 148*128 slots * 960 B = 18 MB) and
+//     software-prefetched one stage ahead; the gains are mirrored to GG[8N][nslots] so that a rejected
+//     line-search trial can be undone without re-running the Riccati sweep.
+//   * LANE REFILL: a lane whose instance has converged writes its outputs and immediately claims the next
+//     unsolved instance from a global queue (warp-aggregated atomicAdd), so a warp never idles on its
+//     slowest instance.  Every round of the warp loop is  [backward | finish+refill+setup | forward].
+//
+// The per-slot functions are B2C_HD so tests/ can run the identical state machine on the host
+// (-DB2C_HOST_EMUL, test-only library).
+#include "mpc_args.cuh"
+
+namespace {
+
+struct SlotMem {
+    double* w;  double* u;  double* ob;  int ss;      // shared strips (host emulation: plain arrays, ss = 1)
+    double* g;  double* gg; int64_t gs;               // global strips, element (f) at f*gs
+};
+#define MW(f)  m.w[(f) * m.ss]
+#define MU(f)  m.u[(f) * m.ss]
+#define MO(f)  m.ob[(f) * m.ss]
+#define MG(f)  m.g[(int64_t)(f) * m.gs]
+#define MGG(f) m.gg[(int64_t)(f) * m.gs]
+
+enum { SLOT_IDLE = 0, SLOT_BWD = 1, SLOT_FWD_GAIN = 2, SLOT_FWD_PLAIN = 3 };
+
+struct SlotState {
+    int64_t inst;
+    int mode, it, ls, st;
+    double alpha, J, dec, z0x, z0y, z0t, lamx, lamy, lamt, max_viol;
+    double x0x, x0t, r0x, r0t;                        // kept for the fallback law
+};
+
+// ----- setup: claim instance i, stage its constants, w = clip(0) ---------------------------------
+B2C_HD void slot_setup(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
+    const int N = a.N, M = a.M;
+    const int64_t B = a.B;
+    s.inst = i; s.it = 0; s.ls = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
+    const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + B + i), x0t = B2C_LDG(a.x0 + 2 * B + i);
+    const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + B + i), r0t = B2C_LDG(a.xref + 2 * B + i);
+    s.x0x = x0x; s.x0t = x0t; s.r0x = r0x; s.r0t = r0t;
+    s.z0x = x0x - r0x; s.z0y = x0y - r0y; s.z0t = b2c_wrap(x0t - r0t);       // :392-401, :421
+    for (int e = 0; e < 3 * M; ++e) MO(e) = B2C_LDG(a.obs + (int64_t)e * B + i);
+    double th_prev = r0t, cum = 0.0;                                          // np.unwrap along the horizon
+    for (int k = 0; k < N; ++k) {
+        const double th_raw = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
+        if (k > 0) cum += unwrap_correction(th_raw - th_prev);
+        th_prev = th_raw;
+        double sn, cs; sincos(th_raw + cum, &sn, &cs);
+        const double uo0 = B2C_LDG(a.uref + (int64_t)(2 * k) * B + i);
+        const double uo1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * B + i);
+        MG(6 * k + 0) = cs * a.dt; MG(6 * k + 1) = sn * a.dt;
+        MG(6 * k + 2) = uo0;       MG(6 * k + 3) = uo1;
+        MG(6 * k + 4) = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
+        MG(6 * k + 5) = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+        MW(2 * k)     = b2c_clip(0.0, -a.v_max - uo0, a.v_max - uo0);
+        MW(2 * k + 1) = b2c_clip(0.0, -a.w_max - uo1, a.w_max - uo1);
+    }
+    s.mode = SLOT_FWD_PLAIN;
+}
+
+// ----- forward sweep -------------------------------------------------------------------------------
+// gain == false: evaluate cost + stage model at the current inputs.
+// gain == true : w+ = clip(w - alpha*kf - K (z+ - z)), rolled out closed loop; W is updated IN PLACE and
+//                the previous inputs are parked in U[8k+6..7] (the model overwrites the gains it just used).
+B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& s, const bool gain,
+                           double& max_viol, double& lamx, double& lamy, double& lamt) {
+    const int N = a.N, M = a.M;
+    double zx = s.z0x, zy = s.z0y, zt = s.z0t;        // new trajectory
+    double ox = zx, oy = zy, ot = zt;                 // old trajectory
+    double J = 0.0, mv = 0.0;
+    const double alpha = s.alpha;
+    double ck = MG(0), sk = MG(1), uo0 = MG(2), uo1 = MG(3), prx = MG(4), pry = MG(5);
+    for (int k = 0; k < N; ++k) {
+        // prefetch the next stage's constants (L2 latency hides behind this stage's arithmetic)
+        const int kn = (k + 1 < N) ? (k + 1) : k;
+        const double nck = MG(6 * kn + 0), nsk = MG(6 * kn + 1), nuo0 = MG(6 * kn + 2), nuo1 = MG(6 * kn + 3);
+        const double nprx = MG(6 * kn + 4), npry = MG(6 * kn + 5);
+        const double wo0 = MW(2 * k), wo1 = MW(2 * k + 1);
+        double w0 = wo0, w1 = wo1;
+        if (gain) {
+            const double dx = zx - ox, dy = zy - oy, dth = zt - ot;
+            w0 = wo0 - alpha * MU(8 * k + 6) - (MU(8 * k + 0) * dx + MU(8 * k + 1) * dy + MU(8 * k + 2) * dth);
+            w1 = wo1 - alpha * MU(8 * k + 7) - (MU(8 * k + 3) * dx + MU(8 * k + 4) * dy + MU(8 * k + 5) * dth);
+            w0 = b2c_clip(w0, -a.v_max - uo0, a.v_max - uo0);
+            w1 = b2c_clip(w1, -a.w_max - uo1, a.w_max - uo1);
+            MW(2 * k) = w0; MW(2 * k + 1) = w1;
+        }
+        double wxx = a.q0, wxy = 0.0, wyy = a.q1;
+        double gx = a.q0 * zx, gy = a.q1 * zy;
+        const double gt = a.q2 * zt;
+        J += a.q0 * zx * zx + a.q1 * zy * zy + a.q2 * zt * zt;
+        for (int mm = 0; mm < M; ++mm) {                  // soft obstacle rows, :439-468
+            const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1);
+            const double d2 = ddx * ddx + ddy * ddy;
+            if (d2 > 1e-4) {                              // dist > 0.01
+                const double inv = B2C_RSQRT(d2);
+                const double nx = ddx * inv, ny = ddy * inv;
+                const double viol = (a.d_safe + MO(3 * mm + 2)) - (d2 * inv + nx * zx + ny * zy);
+                if (viol > 0.0) {
+                    mv = fmax(mv, viol);
+                    J += a.rho * viol * viol;
+                    const double rn0 = a.rho * nx, rn1 = a.rho * ny;
+                    wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
+                    gx -= rn0 * viol; gy -= rn1 * viol;
+                }
+            }
+        }
+        const double ut0 = w0 + uo0, ut1 = w1 + uo1;
+        J += a.r0 * ut0 * ut0 + a.r1 * ut1 * ut1;
+        MU(8 * k + 0) = gx;  MU(8 * k + 1) = gy;  MU(8 * k + 2) = gt;
+        MU(8 * k + 3) = wxx; MU(8 * k + 4) = wxy; MU(8 * k + 5) = wyy;
+        MU(8 * k + 6) = wo0; MU(8 * k + 7) = wo1;
+        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);                       // :425
+        const double a_k = -vr * sk, b_k = vr * ck;
+        const double nzx = zx + a_k * zt + ck * w0, nzy = zy + b_k * zt + sk * w0;
+        const double nox = ox + a_k * ot + ck * wo0, noy = oy + b_k * ot + sk * wo0;
+        zt = zt + a.dt * w1; zx = nzx; zy = nzy;
+        ot = ot + a.dt * wo1; ox = nox; oy = noy;
+        ck = nck; sk = nsk; uo0 = nuo0; uo1 = nuo1; prx = nprx; pry = npry;
+    }
+    J += a.p0 * zx * zx + a.p1 * zy * zy + a.p2 * zt * zt;                       // terminal cost, :412
+    lamx = a.p0 * zx; lamy = a.p1 * zy; lamt = a.p2 * zt;
+    max_viol = mv;
+    return J;
+}
+
+// ----- backward sweep ------------------------------------------------------------------------------
+// Riccati recursion on the stored stage models with the block_size == 1 structure written out
+// (A = I + [0 0 al; 0 0 be; 0 0 0], B = [ck 0; sk 0; 0 dt], Hzz = [wxx wxy 0; wxy wyy 0; 0 0 q2], Huu = R).
+// Gains go to U (over the model they were computed from) and are mirrored to GG.
+B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState& s) {
+    const int N = a.N;
+    const double dt = a.dt;
+    double s00 = a.p0, s01 = 0.0, s02 = 0.0, s11 = a.p1, s12 = 0.0, s22 = a.p2;
+    double v0 = s.lamx, v1 = s.lamy, v2 = s.lamt;     // value-function gradient
+    double l0 = v0, l1 = v1, l2 = v2;                 // true costate
+    double dec = 0.0;
+    double ck = MG(6 * (N - 1) + 0), sk = MG(6 * (N - 1) + 1), uo0 = MG(6 * (N - 1) + 2), uo1 = MG(6 * (N - 1) + 3);
+    for (int j = N - 1; j >= 0; --j) {
+        const int jn = (j > 0) ? (j - 1) : 0;
+        const double nck = MG(6 * jn + 0), nsk = MG(6 * jn + 1), nuo0 = MG(6 * jn + 2), nuo1 = MG(6 * jn + 3);
+        const double gz0 = MU(8 * j + 0), gz1 = MU(8 * j + 1), gz2 = MU(8 * j + 2);
+        const double H0 = MU(8 * j + 3), H1 = MU(8 * j + 4), H3 = MU(8 * j + 5);
+        const double w0 = MW(2 * j), w1 = MW(2 * j + 1);
+        const double gu0 = a.r0 * (w0 + uo0), gu1 = a.r1 * (w1 + uo1);
+        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
+        const double al = -vr * sk, be = vr * ck;
+        // true gradient wrt w_j decides which bounded inputs are frozen; then the costate update
+        const double gt0 = gu0 + ck * l0 + sk * l1;
+        const double gt1 = gu1 + dt * l2;
+        {
+            const double nl2 = gz2 + al * l0 + be * l1 + l2;
+            l0 = gz0 + l0; l1 = gz1 + l1; l2 = nl2;
+        }
+        const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
+        const bool c0 = (w0 <= lb0 && gt0 > 0.0) || (w0 >= ub0 && gt0 < 0.0);
+        const bool c1 = (w1 <= lb1 && gt1 > 0.0) || (w1 >= ub1 && gt1 < 0.0);
+        // third column of S*A
+        const double t0 = al * s00 + be * s01 + s02;
+        const double t1 = al * s01 + be * s11 + s12;
+        const double t2 = al * s02 + be * s12 + s22;
+        const double Q00 = H0 + s00, Q01 = H1 + s01, Q02 = t0;
+        const double Q11 = H3 + s11, Q12 = t1;
+        const double Q22 = a.q2 + al * t0 + be * t1 + t2;
+        double U00 = ck * s00 + sk * s01, U01 = ck * s01 + sk * s11, U02 = ck * t0 + sk * t1;
+        double U10 = dt * s02, U11 = dt * s12, U12 = dt * t2;
+        double R00 = a.r0 + ck * U00 + sk * U01;
+        double R01 = ck * U10 + sk * U11;
+        double R11 = a.r1 + dt * dt * s22;
+        const double qz0 = gz0 + v0, qz1 = gz1 + v1, qz2 = gz2 + al * v0 + be * v1 + v2;
+        double qu0 = gu0 + ck * v0 + sk * v1;
+        double qu1 = gu1 + dt * v2;
+        if (c0) { R00 = 1.0; R01 = 0.0; U00 = 0.0; U01 = 0.0; U02 = 0.0; qu0 = 0.0; }
+        if (c1) { R11 = 1.0; R01 = 0.0; U10 = 0.0; U11 = 0.0; U12 = 0.0; qu1 = 0.0; }
+        const double idet = 1.0 / (R00 * R11 - R01 * R01);
+        const double i00 = R11 * idet, i01 = -R01 * idet, i11 = R00 * idet;
+        const double K00 = i00 * U00 + i01 * U10, K01 = i00 * U01 + i01 * U11, K02 = i00 * U02 + i01 * U12;
+        const double K10 = i01 * U00 + i11 * U10, K11 = i01 * U01 + i11 * U11, K12 = i01 * U02 + i11 * U12;
+        const double k0 = i00 * qu0 + i01 * qu1, k1 = i01 * qu0 + i11 * qu1;
+        MU(8 * j + 0) = K00; MU(8 * j + 1) = K01; MU(8 * j + 2) = K02;
+        MU(8 * j + 3) = K10; MU(8 * j + 4) = K11; MU(8 * j + 5) = K12;
+        MU(8 * j + 6) = k0;  MU(8 * j + 7) = k1;
+        MGG(8 * j + 0) = K00; MGG(8 * j + 1) = K01; MGG(8 * j + 2) = K02;
+        MGG(8 * j + 3) = K10; MGG(8 * j + 4) = K11; MGG(8 * j + 5) = K12;
+        MGG(8 * j + 6) = k0;  MGG(8 * j + 7) = k1;
+        dec += 0.5 * (qu0 * k0 + qu1 * k1);
+        s00 = Q00 - (U00 * K00 + U10 * K10);
+        s01 = Q01 - (U00 * K01 + U10 * K11);
+        s02 = Q02 - (U00 * K02 + U10 * K12);
+        s11 = Q11 - (U01 * K01 + U11 * K11);
+        s12 = Q12 - (U01 * K02 + U11 * K12);
+        s22 = Q22 - (U02 * K02 + U12 * K12);
+        v0 = qz0 - (U00 * k0 + U10 * k1);
+        v1 = qz1 - (U01 * k0 + U11 * k1);
+        v2 = qz2 - (U02 * k0 + U12 * k1);
+        ck = nck; sk = nsk; uo0 = nuo0; uo1 = nuo1;
+    }
+    return dec;
+}
+
+// ----- undo a rejected trial -------------------------------------------------------------------------
+// W <- parked previous inputs; U <- gains from the mirror.  From the MPC_LS_CLOSED-th rejection of an
+// iteration on, the gains are rewritten as the OPEN-LOOP Newton direction of the linear model
+// (d_j = -kf_j - K_j dz_j, dz_{j+1} = A dz_j + B d_j) so that the next trial is Bertsekas' projection
+// arc P[w + alpha d], which descends for small alpha because frozen inputs are decoupled in Quu.
+B2C_HD void slot_restore(const MpcArgs& a, const SlotMem& m, const bool open_loop) {
+    const int N = a.N;
+    double dx = 0.0, dy = 0.0, dth = 0.0;
+    for (int j = 0; j < N; ++j) {
+        MW(2 * j) = MU(8 * j + 6); MW(2 * j + 1) = MU(8 * j + 7);
+        const double K00 = MGG(8 * j + 0), K01 = MGG(8 * j + 1), K02 = MGG(8 * j + 2);
+        const double K10 = MGG(8 * j + 3), K11 = MGG(8 * j + 4), K12 = MGG(8 * j + 5);
+        const double k0 = MGG(8 * j + 6), k1 = MGG(8 * j + 7);
+        if (!open_loop) {
+            MU(8 * j + 0) = K00; MU(8 * j + 1) = K01; MU(8 * j + 2) = K02;
+            MU(8 * j + 3) = K10; MU(8 * j + 4) = K11; MU(8 * j + 5) = K12;
+            MU(8 * j + 6) = k0;  MU(8 * j + 7) = k1;
+        } else {
+            const double d0 = -k0 - (K00 * dx + K01 * dy + K02 * dth);
+            const double d1 = -k1 - (K10 * dx + K11 * dy + K12 * dth);
+            const double ck = MG(6 * j + 0), sk = MG(6 * j + 1);
+            const double vr = b2c_guard_v(MG(6 * j + 2), B2C_GUARD_MPC);
+            const double ndx = dx + (-vr * sk) * dth + ck * d0;
+            const double ndy = dy + (vr * ck) * dth + sk * d0;
+            dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+            for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
+            MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
+        }
+    }
+}
+
+// ----- outputs (:484-522 on success, _get_fallback_solution :316-343 otherwise) -----------------------
+B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
+    const int N = a.N;
+    const int64_t B = a.B, i = s.inst;
+    const double ur00 = MG(2), ur01 = MG(3);
+    double u00, u01, Jout, mv = s.max_viol;
+    const int sc = a.step_count ? a.step_count[i] : a.ramp_up_steps;
+    if (s.st == B2C_OK) {
+        u00 = ur00 + MW(0); u01 = ur01 + MW(1);
+        Jout = s.J;
+        if (a.useq || a.xpred) {                  // add the (wrapped) references back, :497-498
+            double zx = s.z0x, zy = s.z0y, zt = s.z0t;
+            for (int k = 0; k <= N; ++k) {
+                if (a.xpred) {
+                    a.xpred[(int64_t)(3 * k) * B + i]     = zx + B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
+                    a.xpred[(int64_t)(3 * k + 1) * B + i] = zy + B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+                    a.xpred[(int64_t)(3 * k + 2) * B + i] = zt + B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
+                }
+                if (k == N) break;
+                const double wk0 = MW(2 * k), wk1 = MW(2 * k + 1);
+                const double ck = MG(6 * k + 0), sk = MG(6 * k + 1), uo0 = MG(6 * k + 2), uo1 = MG(6 * k + 3);
+                if (a.useq) {
+                    a.useq[(int64_t)(2 * k) * B + i] = wk0 + uo0;
+                    a.useq[(int64_t)(2 * k + 1) * B + i] = wk1 + uo1;
+                }
+                const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
+                const double nzx = zx + (-vr * sk) * zt + ck * wk0, nzy = zy + (vr * ck) * zt + sk * wk0;
+                zt = zt + a.dt * wk1; zx = nzx; zy = nzy;
+            }
+        }
+        if (sc < a.ramp_up_steps) {               // cold-start ramp, :500-507
+            const double lim = a.w_max * ((double)(sc + 1) / (double)a.ramp_up_steps);
+            u01 = b2c_clip(u01, -lim, lim);
+            if (a.useq) a.useq[B + i] = u01;
+        }
+        if (a.step_count) a.step_count[i] = sc + 1;
+    } else {
+        const double e0 = s.x0x - s.r0x, e2 = b2c_wrap(s.x0t - s.r0t);
+        u00 = b2c_clip(ur00 + (-1.0 * e0), -a.v_max, a.v_max);
+        u01 = b2c_clip(ur01 + (-0.5 * e2), -a.w_max, a.w_max);
+        Jout = (double)INFINITY;
+        mv = 0.0;
+        if (a.useq || a.xpred) {
+            const double x0y = B2C_LDG(a.x0 + B + i);
+            for (int k = 0; k <= N; ++k) {
+                if (a.xpred) {
+                    a.xpred[(int64_t)(3 * k) * B + i] = s.x0x;
+                    a.xpred[(int64_t)(3 * k + 1) * B + i] = x0y;
+                    a.xpred[(int64_t)(3 * k + 2) * B + i] = s.x0t;
+                }
+                if (k < N && a.useq) {
+                    a.useq[(int64_t)(2 * k) * B + i] = u00;
+                    a.useq[(int64_t)(2 * k + 1) * B + i] = u01;
+                }
+            }
+        }
+    }
+    a.u0[i] = u00; a.u0[B + i] = u01;
+    a.cost[i] = Jout;
+    if (a.status) a.status[i] = s.st;
+    if (a.iters) a.iters[i] = s.it;
+    if (a.slack_used) a.slack_used[i] = (mv > 1e-6) ? 1 : 0;   // :485
+    s.mode = SLOT_IDLE;
+}
+
+// ----- the per-slot state machine: one call = the lane's share of one phase ---------------------------
+B2C_HD void slot_phase_backward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
+    s.dec = slot_backward(a, m, s);
+    if (!(s.dec < 1e300)) { s.st = B2C_NONFINITE; slot_finish(a, m, s); return; }
+    if (s.dec <= a.tol * fmax(1.0, fabs(s.J))) { s.st = B2C_OK; slot_finish(a, m, s); return; }
+    if (s.it >= a.max_iter) { s.st = B2C_MAXITER; slot_finish(a, m, s); return; }
+    ++s.it; s.alpha = 1.0; s.ls = 0; s.mode = SLOT_FWD_GAIN;
+}
+
+B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
+    double mv, lx, ly, lt;
+    const bool gain = (s.mode == SLOT_FWD_GAIN);
+    const double Jn = slot_forward(a, m, s, gain, mv, lx, ly, lt);
+    if (!gain) {                                  // first evaluation of a fresh instance
+        s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;
+        if (!(a.v_max >= 0.0) || !(a.w_max >= 0.0)) { s.st = B2C_INFEASIBLE; slot_finish(a, m, s); return; }
+        if (!(fabs(Jn) < 1e300)) { s.st = B2C_NONFINITE; slot_finish(a, m, s); return; }
+        s.mode = SLOT_BWD;
+        return;
+    }
+    if (Jn < s.J) {                               // accept
+        s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt; s.mode = SLOT_BWD;
+        return;
+    }
+    s.alpha *= 0.5; ++s.ls;                       // reject: undo, shorten
+    if (s.ls == MPC_LS_CLOSED) s.alpha = 1.0;
+    slot_restore(a, m, s.ls >= MPC_LS_CLOSED);
+    if (s.ls >= MPC_LS_MAX) {                     // rounding floor or stall
+        s.st = (s.dec <= 1e-9 * fmax(1.0, fabs(s.J))) ? B2C_OK : B2C_MAXITER;
+        slot_finish(a, m, s);
+    }
+}
+
+// ----- kernel ---------------------------------------------------------------------------------------
+#ifndef B2C_HOST_EMUL
+__global__ void __launch_bounds__(128, 1)
+k_mpc_slots(const MpcArgs a) {
+    extern __shared__ double smem[];
+    const int tpb = blockDim.x, lane = threadIdx.x & 31;
+    const int64_t slot = (int64_t)blockIdx.x * tpb + threadIdx.x;
+    SlotMem m;
+    m.ss = tpb;
+    m.w = smem + threadIdx.x;
+    m.u = m.w + (size_t)2 * a.N * tpb;
+    m.ob = m.u + (size_t)8 * a.N * tpb;
+    m.gs = a.nslots;
+    m.g = a.scratch + slot;
+    m.gg = m.g + (int64_t)6 * a.N * a.nslots;
+    SlotState s;
+    s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0;
+    s.alpha = s.J = s.dec = s.z0x = s.z0y = s.z0t = s.lamx = s.lamy = s.lamt = s.max_viol = 0.0;
+    s.x0x = s.x0t = s.r0x = s.r0t = 0.0;
+    bool empty = false;
+    const unsigned FULL = 0xffffffffu;
+    for (;;) {
+        if (s.mode == SLOT_BWD) slot_phase_backward(a, m, s);
+        __syncwarp();
+        const bool want = (s.mode == SLOT_IDLE) && !empty;
+        const unsigned need = __ballot_sync(FULL, want);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(a.queue, (unsigned long long)__popc(need));
+            base = __shfl_sync(FULL, base, leader);
+            if (want) {
+                const int64_t id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                if (id < a.B) slot_setup(a, m, s, id);
+            }
+            if ((int64_t)base + __popc(need) >= a.B) empty = true;
+        }
+        if (empty && __all_sync(FULL, s.mode == SLOT_IDLE)) break;
+        __syncwarp();
+        if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward(a, m, s);
+        __syncwarp();
+    }
+}
+#endif
+
+}  // namespace
+
+// shared-memory doubles per slot
+static inline int slot_fields(const MpcArgs& a) { return 10 * a.N + 3 * a.M; }
+
+bool mpc_slots_eligible(const MpcArgs& a, int* tpb_out) {
+    if (a.kind != B2C_MPC_LTV || a.bs != 1 || !a.soft) return false;
+    const size_t cap = 227 * 1024;
+    for (int tpb = 128; tpb >= 32; tpb >>= 1) {
+        if ((size_t)slot_fields(a) * tpb * sizeof(double) <= cap) { *tpb_out = tpb; return true; }
+    }
+    return false;
+}
+
+#ifndef B2C_HOST_EMUL
+int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
+    const size_t smem = (size_t)slot_fields(a) * tpb * sizeof(double);
+    B2C_CUDA(cudaFuncSetAttribute(k_mpc_slots, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    int grid = (int)((a.B + tpb - 1) / tpb);
+    if (grid > ctx->sm_count) grid = ctx->sm_count;
+    a.nslots = (int64_t)grid * tpb;
+    // global strips: G[6N] + GG[8N] doubles per slot, then the queue counter
+    const size_t strip = (size_t)(14 * a.N) * (size_t)a.nslots * sizeof(double);
+    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, strip + 256, false);
+    if (rc) return rc;
+    a.scratch = (double*)ctx->scratch;
+    a.queue = (unsigned long long*)((char*)ctx->scratch + strip);
+    B2C_CUDA(cudaMemsetAsync(a.queue, 0, sizeof(unsigned long long), ctx->stream));
+    k_mpc_slots<<<grid, tpb, smem, ctx->stream>>>(a);
+    B2C_CHECK_LAUNCH(ctx);
+    return 0;
+}
+#else
+int mpc_slots_launch(b2c_ctx*, MpcArgs&, int) { return -1; }
+
+#include <vector>
+// Test-only: the slot state machine on the host, one instance at a time (SoA host pointers).
+extern "C" int b2c_emul_mpc_slots(int64_t B, const b2c_mpc_params* p,
+                                  const double* x0, const double* xref, const double* uref, const double* obs,
+                                  int32_t* step_count, double* u0, double* cost, int32_t* status,
+                                  int32_t* iters, int32_t* slack_used, double* useq, double* xpred) {
+    MpcArgs a;
+    mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
+    int tpb = 0;
+    if (!mpc_slots_eligible(a, &tpb)) return -5;
+    std::vector<double> sm((size_t)slot_fields(a)), gl((size_t)14 * a.N);
+    SlotMem m;
+    m.ss = 1; m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
+    m.gs = 1; m.g = gl.data(); m.gg = m.g + 6 * a.N;
+    for (int64_t i = 0; i < B; ++i) {
+        SlotState s;
+        slot_setup(a, m, s, i);
+        while (s.mode != SLOT_IDLE) {
+            if (s.mode == SLOT_BWD) slot_phase_backward(a, m, s);
+            if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward(a, m, s);
+        }
+    }
+    return 0;
+}
+#endif

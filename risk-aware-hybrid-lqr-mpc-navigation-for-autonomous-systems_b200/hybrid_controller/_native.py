@@ -29,7 +29,7 @@ class B2CError(RuntimeError):
 class MpcParams(C.Structure):
     _fields_ = [("kind", C.c_int32), ("N", C.c_int32), ("M", C.c_int32), ("block_size", C.c_int32),
                 ("soft", C.c_int32), ("max_iter", C.c_int32), ("ramp_up_steps", C.c_int32),
-                ("reserved", C.c_int32),
+                ("engine", C.c_int32),
                 ("Qd", C.c_double * 3), ("Rd", C.c_double * 2), ("Pd", C.c_double * 3),
                 ("d_safe", C.c_double), ("rho", C.c_double), ("v_max", C.c_double),
                 ("w_max", C.c_double), ("dt", C.c_double), ("tol", C.c_double)]
@@ -148,8 +148,9 @@ def default_context(device=-1):
 
 
 def mpc_params(kind, N, M, block_size, Qd, Rd, Pd, d_safe, rho, v_max, w_max, dt, soft=True,
-               max_iter=0, ramp_up_steps=10, tol=0.0):
+               max_iter=0, ramp_up_steps=10, tol=0.0, engine=0):
     p = MpcParams()
+    p.engine = engine
     p.kind, p.N, p.M, p.block_size = kind, N, M, block_size
     p.soft, p.max_iter, p.ramp_up_steps = int(bool(soft)), max_iter, ramp_up_steps
     p.Qd[:] = [float(x) for x in Qd]

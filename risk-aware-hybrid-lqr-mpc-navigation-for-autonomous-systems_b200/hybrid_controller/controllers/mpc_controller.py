@@ -77,6 +77,7 @@ class MPCController:
         self._ramp_up_steps = 10
         self.nx = 3
         self.nu = 2
+        self.engine = 0      # addition: K3 kernel choice (0 auto, 1 general, 2 slot kernel), see include/b2c.h
 
     # -- engine plumbing -------------------------------------------------------------------------
     @property
@@ -90,7 +91,7 @@ class MPCController:
         return nat.mpc_params(kind, self.N, M, self.block_size if kind == nat.MPC_LTV else 1,
                               np.diag(self.Q), np.diag(self.R), np.diag(self.P), self.d_safe,
                               self.slack_penalty, self.v_max, self.omega_max, self.dt, soft=soft,
-                              ramp_up_steps=self._ramp_up_steps)
+                              ramp_up_steps=self._ramp_up_steps, engine=self.engine)
 
     @staticmethod
     def _obs_array(obstacles):

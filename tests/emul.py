@@ -15,7 +15,7 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        srcs = [os.path.join(CSRC, f) for f in ("mpc.cu", "lin_dare.cu", "api.cu", "b2c_common.cuh")]
+        srcs = [os.path.join(CSRC, f) for f in ("mpc.cu", "mpc_slots.cu", "mpc_args.cuh", "lin_dare.cu", "api.cu", "b2c_common.cuh")]
         if not os.path.exists(SO) or any(os.path.getmtime(s) > os.path.getmtime(SO) for s in srcs):
             subprocess.check_call(["make", "-C", CSRC, "emul"], stdout=subprocess.DEVNULL)
         _lib = C.CDLL(SO)
@@ -26,7 +26,7 @@ def _soa(a, B):
     return np.ascontiguousarray(np.asarray(a, float).reshape(B, -1).T)
 
 
-def mpc(params, x0, xref, uref, obs, step_count=None):
+def mpc(params, x0, xref, uref, obs, step_count=None, slots=False):
     from hybrid_controller import _native as nat
     N, M = params.N, params.M
     x0 = np.asarray(x0, float).reshape(-1, 3)
@@ -38,11 +38,11 @@ def mpc(params, x0, xref, uref, obs, step_count=None):
     st, it, sl = (np.empty(B, np.int32) for _ in range(3))
     useq, xpred = np.empty((2 * N, B)), np.empty((3 * (N + 1), B))
     p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
-    f = lib().b2c_emul_mpc
+    f = lib().b2c_emul_mpc_slots if slots else lib().b2c_emul_mpc
     f.argtypes = [C.c_int64, C.POINTER(nat.MpcParams)] + [C.c_void_p] * 12
     rc = f(B, C.byref(params), p(sx0), p(sxr), p(sur), p(sob), p(sc), p(u0), p(cost), p(st), p(it),
            p(sl), p(useq), p(xpred))
-    assert rc == 0
+    assert rc == 0, rc
     return dict(u0=u0.T.copy(), cost=cost, status=st, iters=it, slack_used=sl,
                 useq=useq.T.reshape(B, N, 2).copy(), xpred=xpred.T.reshape(B, N + 1, 3).copy(),
                 step_count=sc)

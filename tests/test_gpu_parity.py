@@ -197,13 +197,16 @@ def _violations(mpc, x0, xr, ur, ob, out, b, bs=1):
     return max(box, 0.0), J
 
 
-def test_mpc_config4_vs_oracle(hc):
-    """Config 4 shape (N=20, M=5, block 1): 1024-instance subsample against the exact oracle."""
+@pytest.mark.parametrize("engine", [1, 2])
+def test_mpc_config4_vs_oracle(hc, engine):
+    """Config 4 shape (N=20, M=5, block 1): 1024-instance subsample against the exact oracle,
+    through both K3 kernels (1 = general HBM-scratch kernel, 2 = persistent slot kernel)."""
     from hybrid_controller.controllers.mpc_controller import MPCController
     from hybrid_controller import workloads as wl
     from oracle import mpc_qp
     B = 1024
     mpc = MPCController(horizon=20, block_size=1, **wl.SIM_MPC)
+    mpc.engine = engine
     x0, xr, ur, ob = wl.config4_instances(B, N=20, seed=0)
     out = mpc.solve_with_ltv_batch(x0, xr, ur, ob)
     assert (out["status"] == 0).all()
@@ -327,6 +330,34 @@ def test_mpc_ramp_fallback_and_edge_cases(hc):
     assert abs(sol.cost - o["cost"]) <= 1e-6 * abs(o["cost"])
     with pytest.raises(IndexError):
         mpc.solve_with_ltv(xr2[0], xr2[:4], ur2[:3], [])
+
+
+@pytest.mark.parametrize("N,M,B", [(20, 5, 20000), (6, 3, 300), (10, 0, 77), (1, 2, 33), (40, 5, 5000), (85, 2, 700)])
+def test_mpc_engines_agree(hc, N, M, B):
+    """The slot kernel (shared-memory scratch, lane refill; 128 / 64 / 32 slots per CTA depending on N)
+    and the general kernel run the same method: same iteration counts, results equal to rounding.
+    Includes ragged batch sizes, per-instance ramp counters and a NaN instance (fallback law)."""
+    from hybrid_controller.controllers.mpc_controller import MPCController
+    from hybrid_controller import workloads as wl
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=N + M, obstacles=wl.DENSE_OBSTACLES[:M],
+                                          pos_jitter=0.15, th_jitter=0.4)
+    x0[B // 2, 1] = np.nan
+    sc = (np.arange(B) % 13).astype(np.int32)
+    outs = []
+    for engine in (1, 2):
+        mpc = MPCController(horizon=N, block_size=1, **wl.SIM_MPC)
+        mpc.engine = engine
+        outs.append(mpc.solve_with_ltv_batch(x0, xr, ur, ob, step_count=sc.copy()))
+    a, b = outs
+    assert np.array_equal(a["status"], b["status"]) and a["status"][B // 2] != 0 and (a["status"] != 0).sum() == 1
+    assert np.array_equal(a["step_count"], b["step_count"]) and np.array_equal(a["slack_used"], b["slack_used"])
+    assert np.abs(a["iters"] - b["iters"]).max() <= 1
+    ok = a["status"] == 0
+    assert np.abs(a["u0"] - b["u0"]).max() <= 1e-9 and np.abs(a["useq"] - b["useq"]).max() <= 1e-9
+    assert np.abs(a["xpred"][ok] - b["xpred"][ok]).max() <= 1e-9
+    assert np.array_equal(a["xpred"][~ok], b["xpred"][~ok], equal_nan=True)
+    assert (np.abs(a["cost"][ok] - b["cost"][ok]) <= 1e-10 * np.abs(a["cost"][ok])).all()
+    assert np.isinf(b["cost"][~ok]).all()
 
 
 def test_mpc_full_size_properties(hc):

@@ -85,6 +85,47 @@ def test_emul_mpc_vs_oracle(N, bs, M):
         assert np.abs(out["xpred"][b] - o["predicted_states"]).max() <= 1e-5
 
 
+@pytest.mark.parametrize("N,M", [(20, 5), (6, 3), (10, 0), (1, 2), (40, 5)])
+def test_emul_slot_state_machine_vs_oracle_and_general(N, M):
+    """The slot kernel's per-lane state machine (mpc_slots.cu: union gains/model storage, in-place input
+    update, undo of rejected trials from the gain mirror) run on the host, against the oracle and
+    against the general kernel's per-instance code."""
+    from hybrid_controller import workloads as wl
+    B = 96
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=N * 7 + M, obstacles=wl.DENSE_OBSTACLES[:M],
+                                          pos_jitter=0.2, th_jitter=0.5)
+    x0[5, 0] = np.nan
+    sc = (np.arange(B) % 12).astype(np.int32)
+    out = emul.mpc(_params(N, M, 1), x0, xr, ur, ob, step_count=sc, slots=True)
+    gen = emul.mpc(_params(N, M, 1), x0, xr, ur, ob, step_count=sc)
+    assert np.array_equal(out["status"], gen["status"]) and out["status"][5] != 0 and (out["status"] != 0).sum() == 1
+    assert np.array_equal(out["iters"], gen["iters"]) and np.array_equal(out["step_count"], gen["step_count"])
+    assert np.isinf(out["cost"][5]) and np.array_equal(out["u0"][5], gen["u0"][5])
+    prm = dict(MPC_PRM20, N=N, block_size=1)
+    for b in range(B):
+        if b == 5:
+            continue
+        assert np.abs(out["u0"][b] - gen["u0"][b]).max() <= 1e-10
+        o = mpc_qp.solve_with_ltv(x0[b], xr[b], ur[b], ob[b], step_count=int(sc[b]), **prm)
+        assert np.abs(out["u0"][b] - o["optimal_control"]).max() <= 1e-4
+        assert abs(out["cost"][b] - o["cost"]) <= 1e-6 * abs(o["cost"])
+        assert bool(out["slack_used"][b]) == o["slack_used"]
+        assert np.abs(out["useq"][b] - o["control_sequence"]).max() <= 1e-4
+        assert np.abs(out["xpred"][b] - o["predicted_states"]).max() <= 1e-5
+
+
+def test_emul_slot_rejected_trials_are_undone():
+    """Instances whose line search rejects trials (incl. the projection-arc fallback) take the
+    restore path of the slot kernel; the result must still equal the general kernel's."""
+    from hybrid_controller import workloads as wl
+    x0, xr, ur, ob = wl.config4_instances(4096, N=20, seed=0)
+    a = emul.mpc(_params(20, 5, 1), x0, xr, ur, ob)
+    b = emul.mpc(_params(20, 5, 1), x0, xr, ur, ob, slots=True)
+    assert (b["status"] == 0).all() and np.array_equal(a["iters"], b["iters"]) and a["iters"].max() >= 8
+    assert np.abs(a["u0"] - b["u0"]).max() <= 1e-10 and np.abs(a["useq"] - b["useq"]).max() <= 1e-10
+    assert (np.abs(a["cost"] - b["cost"]) <= 1e-12 * np.abs(a["cost"])).all()
+
+
 def test_emul_mpc_g_mpc_golden(golden):
     g = golden["g_mpc"]
     traj = lin_dare.figure8(20.0)
