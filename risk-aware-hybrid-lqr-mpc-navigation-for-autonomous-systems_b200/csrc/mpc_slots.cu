@@ -23,14 +23,34 @@
 namespace {
 
 struct SlotMem {
-    double* w;  double* u;  double* ob;  int ss;      // shared strips (host emulation: plain arrays, ss = 1)
-    double* g;  double* gg; int64_t gs;               // global strips, element (f) at f*gs
+    double* w;  double* u;  double* ob;               // shared strips, element (f) at f*SS (host emulation: SS = 1)
+    double* g;  double* gg; int64_t gs;               // global strips: stage k of this slot at g + k*6*gs / gg + k*8*gs
 };
-#define MW(f)  m.w[(f) * m.ss]
-#define MU(f)  m.u[(f) * m.ss]
-#define MO(f)  m.ob[(f) * m.ss]
-#define MG(f)  m.g[(int64_t)(f) * m.gs]
-#define MGG(f) m.gg[(int64_t)(f) * m.gs]
+// 16-byte vector access to the global strips (6 resp. 8 contiguous doubles per stage and slot)
+struct Stage6 { double ck, sk, uo0, uo1, prx, pry; };
+B2C_HD Stage6 g_load(const SlotMem& m, int k) {
+    const double2* p = reinterpret_cast<const double2*>(m.g + (int64_t)k * 6 * m.gs);
+    const double2 a = p[0], b = p[1], c = p[2];
+    return Stage6{a.x, a.y, b.x, b.y, c.x, c.y};
+}
+B2C_HD void g_load4(const SlotMem& m, int k, double& ck, double& sk, double& uo0, double& uo1) {
+    const double2* p = reinterpret_cast<const double2*>(m.g + (int64_t)k * 6 * m.gs);
+    const double2 a = p[0], b = p[1];
+    ck = a.x; sk = a.y; uo0 = b.x; uo1 = b.y;
+}
+B2C_HD void g_store(const SlotMem& m, int k, double ck, double sk, double uo0, double uo1, double prx, double pry) {
+    double2* p = reinterpret_cast<double2*>(m.g + (int64_t)k * 6 * m.gs);
+    p[0] = make_double2(ck, sk); p[1] = make_double2(uo0, uo1); p[2] = make_double2(prx, pry);
+}
+B2C_HD void gg_store(const SlotMem& m, int j, double K00, double K01, double K02, double K10, double K11,
+                     double K12, double k0, double k1) {
+    double2* p = reinterpret_cast<double2*>(m.gg + (int64_t)j * 8 * m.gs);
+    p[0] = make_double2(K00, K01); p[1] = make_double2(K02, K10); p[2] = make_double2(K11, K12);
+    p[3] = make_double2(k0, k1);
+}
+#define MW(f)  m.w[(f) * SS]
+#define MU(f)  m.u[(f) * SS]
+#define MO(f)  m.ob[(f) * SS]
 
 enum { SLOT_IDLE = 0, SLOT_BWD = 1, SLOT_FWD_GAIN = 2, SLOT_FWD_PLAIN = 3 };
 
@@ -42,50 +62,88 @@ struct SlotState {
 };
 
 // ----- setup: claim instance i, stage its constants, w = clip(0) ---------------------------------
+// Two passes so that the instance's input loads (HBM, partially coalesced: lanes that refill in the
+// same round hold consecutive instance ids) are all in flight together: pass 1 copies the raw rows
+// into the (still unused) U strip, pass 2 does the unwrap / sincos arithmetic from shared memory.
+template <int SS, int MT>
 B2C_HD void slot_setup(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
-    const int N = a.N, M = a.M;
+    const int N = a.N, M = (MT >= 0) ? MT : a.M;
     const int64_t B = a.B;
     s.inst = i; s.it = 0; s.ls = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
     const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + B + i), x0t = B2C_LDG(a.x0 + 2 * B + i);
     const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + B + i), r0t = B2C_LDG(a.xref + 2 * B + i);
+#pragma unroll 4
+    for (int k = 0; k < N; ++k) {
+        MU(8 * k + 0) = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
+        MU(8 * k + 1) = B2C_LDG(a.uref + (int64_t)(2 * k) * B + i);
+        MU(8 * k + 2) = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * B + i);
+        MU(8 * k + 3) = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
+        MU(8 * k + 4) = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+    }
+    for (int e = 0; e < M; ++e) {                 // obstacle strip: x, y, d_safe + r
+        MO(3 * e)     = B2C_LDG(a.obs + (int64_t)(3 * e) * B + i);
+        MO(3 * e + 1) = B2C_LDG(a.obs + (int64_t)(3 * e + 1) * B + i);
+        MO(3 * e + 2) = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * e + 2) * B + i);
+    }
     s.x0x = x0x; s.x0t = x0t; s.r0x = r0x; s.r0t = r0t;
     s.z0x = x0x - r0x; s.z0y = x0y - r0y; s.z0t = b2c_wrap(x0t - r0t);       // :392-401, :421
-    for (int e = 0; e < 3 * M; ++e) MO(e) = B2C_LDG(a.obs + (int64_t)e * B + i);
     double th_prev = r0t, cum = 0.0;                                          // np.unwrap along the horizon
     for (int k = 0; k < N; ++k) {
-        const double th_raw = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
+        const double th_raw = MU(8 * k + 0), uo0 = MU(8 * k + 1), uo1 = MU(8 * k + 2);
         if (k > 0) cum += unwrap_correction(th_raw - th_prev);
         th_prev = th_raw;
         double sn, cs; sincos(th_raw + cum, &sn, &cs);
-        const double uo0 = B2C_LDG(a.uref + (int64_t)(2 * k) * B + i);
-        const double uo1 = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * B + i);
-        MG(6 * k + 0) = cs * a.dt; MG(6 * k + 1) = sn * a.dt;
-        MG(6 * k + 2) = uo0;       MG(6 * k + 3) = uo1;
-        MG(6 * k + 4) = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
-        MG(6 * k + 5) = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+        g_store(m, k, cs * a.dt, sn * a.dt, uo0, uo1, MU(8 * k + 3), MU(8 * k + 4));
         MW(2 * k)     = b2c_clip(0.0, -a.v_max - uo0, a.v_max - uo0);
         MW(2 * k + 1) = b2c_clip(0.0, -a.w_max - uo1, a.w_max - uo1);
     }
     s.mode = SLOT_FWD_PLAIN;
 }
 
+// one soft obstacle row, exact arithmetic (:439-468): accumulates cost / gradient / Hessian if violated
+B2C_HD void slot_row(const MpcArgs& a, double ddx, double ddy, double d2, double c, double zx, double zy,
+                     double& J, double& mv, double& gx, double& gy, double& wxx, double& wxy, double& wyy) {
+    const double inv = B2C_RSQRT(d2);
+    const double nx = ddx * inv, ny = ddy * inv;
+    const double viol = c - (d2 * inv + nx * zx + ny * zy);
+    if (viol > 0.0) {
+        mv = fmax(mv, viol);
+        J += a.rho * viol * viol;
+        const double rn0 = a.rho * nx, rn1 = a.rho * ny;
+        wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
+        gx -= rn0 * viol; gy -= rn1 * viol;
+    }
+}
+
 // ----- forward sweep -------------------------------------------------------------------------------
 // gain == false: evaluate cost + stage model at the current inputs.
 // gain == true : w+ = clip(w - alpha*kf - K (z+ - z)), rolled out closed loop; W is updated IN PLACE and
 //                the previous inputs are parked in U[8k+6..7] (the model overwrites the gains it just used).
+// Obstacle rows: row (k,m) is violated iff  c*dist > q  with  q = d2 + dd.dz  (both sides of
+// c - (dist + n.dz) > 0 multiplied by dist), i.e. iff  c|c|*d2 > q|q| -- no square root.  All M tests of a
+// stage are independent (they pipeline); only rows that pass take the rsqrt path.
+template <int SS, int MT>
 B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& s, const bool gain,
                            double& max_viol, double& lamx, double& lamy, double& lamt) {
-    const int N = a.N, M = a.M;
+    const int N = a.N, M = (MT >= 0) ? MT : a.M;
+    constexpr int MR = (MT > 0) ? MT : 1;
+    double OX[MR], OY[MR], OC[MR], OCC[MR];
+    if (MT > 0) {
+#pragma unroll
+        for (int mm = 0; mm < MR; ++mm) {
+            OX[mm] = MO(3 * mm); OY[mm] = MO(3 * mm + 1); OC[mm] = MO(3 * mm + 2);
+            OCC[mm] = OC[mm] * fabs(OC[mm]);
+        }
+    }
     double zx = s.z0x, zy = s.z0y, zt = s.z0t;        // new trajectory
     double ox = zx, oy = zy, ot = zt;                 // old trajectory
     double J = 0.0, mv = 0.0;
-    const double alpha = s.alpha;
-    double ck = MG(0), sk = MG(1), uo0 = MG(2), uo1 = MG(3), prx = MG(4), pry = MG(5);
+    const double alpha = gain ? s.alpha : 0.0;
+    Stage6 cur = g_load(m, 0), nxt = g_load(m, (N > 1) ? 1 : 0);
     for (int k = 0; k < N; ++k) {
-        // prefetch the next stage's constants (L2 latency hides behind this stage's arithmetic)
-        const int kn = (k + 1 < N) ? (k + 1) : k;
-        const double nck = MG(6 * kn + 0), nsk = MG(6 * kn + 1), nuo0 = MG(6 * kn + 2), nuo1 = MG(6 * kn + 3);
-        const double nprx = MG(6 * kn + 4), npry = MG(6 * kn + 5);
+        // prefetch the constants two stages ahead (L2 latency hides behind two stages of arithmetic)
+        const Stage6 nn = g_load(m, (k + 2 < N) ? (k + 2) : (N - 1));
+        const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1, prx = cur.prx, pry = cur.pry;
         const double wo0 = MW(2 * k), wo1 = MW(2 * k + 1);
         double w0 = wo0, w1 = wo1;
         if (gain) {
@@ -100,20 +158,31 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
         double gx = a.q0 * zx, gy = a.q1 * zy;
         const double gt = a.q2 * zt;
         J += a.q0 * zx * zx + a.q1 * zy * zy + a.q2 * zt * zt;
-        for (int mm = 0; mm < M; ++mm) {                  // soft obstacle rows, :439-468
-            const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1);
-            const double d2 = ddx * ddx + ddy * ddy;
-            if (d2 > 1e-4) {                              // dist > 0.01
-                const double inv = B2C_RSQRT(d2);
-                const double nx = ddx * inv, ny = ddy * inv;
-                const double viol = (a.d_safe + MO(3 * mm + 2)) - (d2 * inv + nx * zx + ny * zy);
-                if (viol > 0.0) {
-                    mv = fmax(mv, viol);
-                    J += a.rho * viol * viol;
-                    const double rn0 = a.rho * nx, rn1 = a.rho * ny;
-                    wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
-                    gx -= rn0 * viol; gy -= rn1 * viol;
+        if (MT > 0) {
+            unsigned hit = 0;
+#pragma unroll
+            for (int mm = 0; mm < MR; ++mm) {
+                const double ddx = prx - OX[mm], ddy = pry - OY[mm];
+                const double d2 = ddx * ddx + ddy * ddy;
+                const double q = d2 + ddx * zx + ddy * zy;
+                if ((d2 > 1e-4) && (OCC[mm] * d2 > q * fabs(q))) hit |= (1u << mm);
+            }
+            if (hit) {
+#pragma unroll
+                for (int mm = 0; mm < MR; ++mm) {
+                    if (hit & (1u << mm)) {
+                        const double ddx = prx - OX[mm], ddy = pry - OY[mm];
+                        slot_row(a, ddx, ddy, ddx * ddx + ddy * ddy, OC[mm], zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
+                    }
                 }
+            }
+        } else if (MT < 0) {
+            for (int mm = 0; mm < M; ++mm) {
+                const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1), c = MO(3 * mm + 2);
+                const double d2 = ddx * ddx + ddy * ddy;
+                const double q = d2 + ddx * zx + ddy * zy;
+                if ((d2 > 1e-4) && (c * fabs(c) * d2 > q * fabs(q)))
+                    slot_row(a, ddx, ddy, d2, c, zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
             }
         }
         const double ut0 = w0 + uo0, ut1 = w1 + uo1;
@@ -127,7 +196,7 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
         const double nox = ox + a_k * ot + ck * wo0, noy = oy + b_k * ot + sk * wo0;
         zt = zt + a.dt * w1; zx = nzx; zy = nzy;
         ot = ot + a.dt * wo1; ox = nox; oy = noy;
-        ck = nck; sk = nsk; uo0 = nuo0; uo1 = nuo1; prx = nprx; pry = npry;
+        cur = nxt; nxt = nn;
     }
     J += a.p0 * zx * zx + a.p1 * zy * zy + a.p2 * zt * zt;                       // terminal cost, :412
     lamx = a.p0 * zx; lamy = a.p1 * zy; lamt = a.p2 * zt;
@@ -139,6 +208,7 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
 // Riccati recursion on the stored stage models with the block_size == 1 structure written out
 // (A = I + [0 0 al; 0 0 be; 0 0 0], B = [ck 0; sk 0; 0 dt], Hzz = [wxx wxy 0; wxy wyy 0; 0 0 q2], Huu = R).
 // Gains go to U (over the model they were computed from) and are mirrored to GG.
+template <int SS, int MT>
 B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState& s) {
     const int N = a.N;
     const double dt = a.dt;
@@ -146,10 +216,12 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     double v0 = s.lamx, v1 = s.lamy, v2 = s.lamt;     // value-function gradient
     double l0 = v0, l1 = v1, l2 = v2;                 // true costate
     double dec = 0.0;
-    double ck = MG(6 * (N - 1) + 0), sk = MG(6 * (N - 1) + 1), uo0 = MG(6 * (N - 1) + 2), uo1 = MG(6 * (N - 1) + 3);
+    double ck, sk, uo0, uo1, nck, nsk, nuo0, nuo1;
+    g_load4(m, N - 1, ck, sk, uo0, uo1);
+    g_load4(m, (N > 1) ? (N - 2) : 0, nck, nsk, nuo0, nuo1);
     for (int j = N - 1; j >= 0; --j) {
-        const int jn = (j > 0) ? (j - 1) : 0;
-        const double nck = MG(6 * jn + 0), nsk = MG(6 * jn + 1), nuo0 = MG(6 * jn + 2), nuo1 = MG(6 * jn + 3);
+        double pck, psk, puo0, puo1;                  // two stages ahead
+        g_load4(m, (j > 1) ? (j - 2) : 0, pck, psk, puo0, puo1);
         const double gz0 = MU(8 * j + 0), gz1 = MU(8 * j + 1), gz2 = MU(8 * j + 2);
         const double H0 = MU(8 * j + 3), H1 = MU(8 * j + 4), H3 = MU(8 * j + 5);
         const double w0 = MW(2 * j), w1 = MW(2 * j + 1);
@@ -191,9 +263,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         MU(8 * j + 0) = K00; MU(8 * j + 1) = K01; MU(8 * j + 2) = K02;
         MU(8 * j + 3) = K10; MU(8 * j + 4) = K11; MU(8 * j + 5) = K12;
         MU(8 * j + 6) = k0;  MU(8 * j + 7) = k1;
-        MGG(8 * j + 0) = K00; MGG(8 * j + 1) = K01; MGG(8 * j + 2) = K02;
-        MGG(8 * j + 3) = K10; MGG(8 * j + 4) = K11; MGG(8 * j + 5) = K12;
-        MGG(8 * j + 6) = k0;  MGG(8 * j + 7) = k1;
+        gg_store(m, j, K00, K01, K02, K10, K11, K12, k0, k1);
         dec += 0.5 * (qu0 * k0 + qu1 * k1);
         s00 = Q00 - (U00 * K00 + U10 * K10);
         s01 = Q01 - (U00 * K01 + U10 * K11);
@@ -205,46 +275,56 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         v1 = qz1 - (U01 * k0 + U11 * k1);
         v2 = qz2 - (U02 * k0 + U12 * k1);
         ck = nck; sk = nsk; uo0 = nuo0; uo1 = nuo1;
+        nck = pck; nsk = psk; nuo0 = puo0; nuo1 = puo1;
     }
     return dec;
 }
 
 // ----- undo a rejected trial -------------------------------------------------------------------------
-// W <- parked previous inputs; U <- gains from the mirror.  From the MPC_LS_CLOSED-th rejection of an
-// iteration on, the gains are rewritten as the OPEN-LOOP Newton direction of the linear model
-// (d_j = -kf_j - K_j dz_j, dz_{j+1} = A dz_j + B d_j) so that the next trial is Bertsekas' projection
-// arc P[w + alpha d], which descends for small alpha because frozen inputs are decoupled in Quu.
+// W <- parked previous inputs; U <- gains from the mirror (independent loads, unrolled so they overlap).
+// From the MPC_LS_CLOSED-th rejection of an iteration on, the gains are then rewritten as the OPEN-LOOP
+// Newton direction of the linear model (d_j = -kf_j - K_j dz_j, dz_{j+1} = A dz_j + B d_j) so that the
+// next trial is Bertsekas' projection arc P[w + alpha d], which descends for small alpha because frozen
+// inputs are decoupled in Quu.
+template <int SS, int MT>
 B2C_HD void slot_restore(const MpcArgs& a, const SlotMem& m, const bool open_loop) {
     const int N = a.N;
-    double dx = 0.0, dy = 0.0, dth = 0.0;
+#pragma unroll 2
     for (int j = 0; j < N; ++j) {
         MW(2 * j) = MU(8 * j + 6); MW(2 * j + 1) = MU(8 * j + 7);
-        const double K00 = MGG(8 * j + 0), K01 = MGG(8 * j + 1), K02 = MGG(8 * j + 2);
-        const double K10 = MGG(8 * j + 3), K11 = MGG(8 * j + 4), K12 = MGG(8 * j + 5);
-        const double k0 = MGG(8 * j + 6), k1 = MGG(8 * j + 7);
-        if (!open_loop) {
-            MU(8 * j + 0) = K00; MU(8 * j + 1) = K01; MU(8 * j + 2) = K02;
-            MU(8 * j + 3) = K10; MU(8 * j + 4) = K11; MU(8 * j + 5) = K12;
-            MU(8 * j + 6) = k0;  MU(8 * j + 7) = k1;
-        } else {
-            const double d0 = -k0 - (K00 * dx + K01 * dy + K02 * dth);
-            const double d1 = -k1 - (K10 * dx + K11 * dy + K12 * dth);
-            const double ck = MG(6 * j + 0), sk = MG(6 * j + 1);
-            const double vr = b2c_guard_v(MG(6 * j + 2), B2C_GUARD_MPC);
-            const double ndx = dx + (-vr * sk) * dth + ck * d0;
-            const double ndy = dy + (vr * ck) * dth + sk * d0;
-            dth = dth + a.dt * d1; dx = ndx; dy = ndy;
-            for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
-            MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
-        }
+        const double2* p = reinterpret_cast<const double2*>(m.gg + (int64_t)j * 8 * m.gs);
+        const double2 q0 = p[0], q1 = p[1], q2 = p[2], q3 = p[3];
+        MU(8 * j + 0) = q0.x; MU(8 * j + 1) = q0.y; MU(8 * j + 2) = q1.x;
+        MU(8 * j + 3) = q1.y; MU(8 * j + 4) = q2.x; MU(8 * j + 5) = q2.y;
+        MU(8 * j + 6) = q3.x; MU(8 * j + 7) = q3.y;
+    }
+    if (!open_loop) return;
+    double dx = 0.0, dy = 0.0, dth = 0.0;
+    double ck, sk, uo0, uo1;
+    g_load4(m, 0, ck, sk, uo0, uo1);
+    for (int j = 0; j < N; ++j) {
+        double nck, nsk, nuo0;
+        g_load4(m, (j + 1 < N) ? (j + 1) : j, nck, nsk, nuo0, uo1);
+        const double d0 = -MU(8 * j + 6) - (MU(8 * j + 0) * dx + MU(8 * j + 1) * dy + MU(8 * j + 2) * dth);
+        const double d1 = -MU(8 * j + 7) - (MU(8 * j + 3) * dx + MU(8 * j + 4) * dy + MU(8 * j + 5) * dth);
+        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
+        const double ndx = dx + (-vr * sk) * dth + ck * d0;
+        const double ndy = dy + (vr * ck) * dth + sk * d0;
+        dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+#pragma unroll
+        for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
+        MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
+        ck = nck; sk = nsk; uo0 = nuo0;
     }
 }
 
 // ----- outputs (:484-522 on success, _get_fallback_solution :316-343 otherwise) -----------------------
+template <int SS, int MT>
 B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
     const int N = a.N;
     const int64_t B = a.B, i = s.inst;
-    const double ur00 = MG(2), ur01 = MG(3);
+    const Stage6 g0 = g_load(m, 0);
+    const double ur00 = g0.uo0, ur01 = g0.uo1;
     double u00, u01, Jout, mv = s.max_viol;
     const int sc = a.step_count ? a.step_count[i] : a.ramp_up_steps;
     if (s.st == B2C_OK) {
@@ -260,7 +340,8 @@ B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
                 }
                 if (k == N) break;
                 const double wk0 = MW(2 * k), wk1 = MW(2 * k + 1);
-                const double ck = MG(6 * k + 0), sk = MG(6 * k + 1), uo0 = MG(6 * k + 2), uo1 = MG(6 * k + 3);
+                double ck, sk, uo0, uo1;
+                g_load4(m, k, ck, sk, uo0, uo1);
                 if (a.useq) {
                     a.useq[(int64_t)(2 * k) * B + i] = wk0 + uo0;
                     a.useq[(int64_t)(2 * k + 1) * B + i] = wk1 + uo1;
@@ -306,22 +387,24 @@ B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
 }
 
 // ----- the per-slot state machine: one call = the lane's share of one phase ---------------------------
+template <int SS, int MT>
 B2C_HD void slot_phase_backward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
-    s.dec = slot_backward(a, m, s);
-    if (!(s.dec < 1e300)) { s.st = B2C_NONFINITE; slot_finish(a, m, s); return; }
-    if (s.dec <= a.tol * fmax(1.0, fabs(s.J))) { s.st = B2C_OK; slot_finish(a, m, s); return; }
-    if (s.it >= a.max_iter) { s.st = B2C_MAXITER; slot_finish(a, m, s); return; }
+    s.dec = slot_backward<SS, MT>(a, m, s);
+    if (!(s.dec < 1e300)) { s.st = B2C_NONFINITE; slot_finish<SS, MT>(a, m, s); return; }
+    if (s.dec <= a.tol * fmax(1.0, fabs(s.J))) { s.st = B2C_OK; slot_finish<SS, MT>(a, m, s); return; }
+    if (s.it >= a.max_iter) { s.st = B2C_MAXITER; slot_finish<SS, MT>(a, m, s); return; }
     ++s.it; s.alpha = 1.0; s.ls = 0; s.mode = SLOT_FWD_GAIN;
 }
 
+template <int SS, int MT>
 B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
     double mv, lx, ly, lt;
     const bool gain = (s.mode == SLOT_FWD_GAIN);
-    const double Jn = slot_forward(a, m, s, gain, mv, lx, ly, lt);
+    const double Jn = slot_forward<SS, MT>(a, m, s, gain, mv, lx, ly, lt);
     if (!gain) {                                  // first evaluation of a fresh instance
         s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;
-        if (!(a.v_max >= 0.0) || !(a.w_max >= 0.0)) { s.st = B2C_INFEASIBLE; slot_finish(a, m, s); return; }
-        if (!(fabs(Jn) < 1e300)) { s.st = B2C_NONFINITE; slot_finish(a, m, s); return; }
+        if (!(a.v_max >= 0.0) || !(a.w_max >= 0.0)) { s.st = B2C_INFEASIBLE; slot_finish<SS, MT>(a, m, s); return; }
+        if (!(fabs(Jn) < 1e300)) { s.st = B2C_NONFINITE; slot_finish<SS, MT>(a, m, s); return; }
         s.mode = SLOT_BWD;
         return;
     }
@@ -331,28 +414,29 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
     }
     s.alpha *= 0.5; ++s.ls;                       // reject: undo, shorten
     if (s.ls == MPC_LS_CLOSED) s.alpha = 1.0;
-    slot_restore(a, m, s.ls >= MPC_LS_CLOSED);
+    slot_restore<SS, MT>(a, m, s.ls >= MPC_LS_CLOSED);
     if (s.ls >= MPC_LS_MAX) {                     // rounding floor or stall
         s.st = (s.dec <= 1e-9 * fmax(1.0, fabs(s.J))) ? B2C_OK : B2C_MAXITER;
-        slot_finish(a, m, s);
+        slot_finish<SS, MT>(a, m, s);
     }
 }
 
 // ----- kernel ---------------------------------------------------------------------------------------
 #ifndef B2C_HOST_EMUL
-__global__ void __launch_bounds__(128, 1)
+template <int SS, int MT>
+__global__ void __launch_bounds__(SS, 1)
 k_mpc_slots(const MpcArgs a) {
     extern __shared__ double smem[];
-    const int tpb = blockDim.x, lane = threadIdx.x & 31;
+    constexpr int tpb = SS;
+    const int lane = threadIdx.x & 31;
     const int64_t slot = (int64_t)blockIdx.x * tpb + threadIdx.x;
     SlotMem m;
-    m.ss = tpb;
     m.w = smem + threadIdx.x;
     m.u = m.w + (size_t)2 * a.N * tpb;
     m.ob = m.u + (size_t)8 * a.N * tpb;
     m.gs = a.nslots;
-    m.g = a.scratch + slot;
-    m.gg = m.g + (int64_t)6 * a.N * a.nslots;
+    m.g = a.scratch + slot * 6;
+    m.gg = a.scratch + (int64_t)6 * a.N * a.nslots + slot * 8;
     SlotState s;
     s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0;
     s.alpha = s.J = s.dec = s.z0x = s.z0y = s.z0t = s.lamx = s.lamy = s.lamt = s.max_viol = 0.0;
@@ -360,7 +444,7 @@ k_mpc_slots(const MpcArgs a) {
     bool empty = false;
     const unsigned FULL = 0xffffffffu;
     for (;;) {
-        if (s.mode == SLOT_BWD) slot_phase_backward(a, m, s);
+        if (s.mode == SLOT_BWD) slot_phase_backward<SS, MT>(a, m, s);
         __syncwarp();
         const bool want = (s.mode == SLOT_IDLE) && !empty;
         const unsigned need = __ballot_sync(FULL, want);
@@ -371,13 +455,13 @@ k_mpc_slots(const MpcArgs a) {
             base = __shfl_sync(FULL, base, leader);
             if (want) {
                 const int64_t id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
-                if (id < a.B) slot_setup(a, m, s, id);
+                if (id < a.B) slot_setup<SS, MT>(a, m, s, id);
             }
             if ((int64_t)base + __popc(need) >= a.B) empty = true;
         }
         if (empty && __all_sync(FULL, s.mode == SLOT_IDLE)) break;
         __syncwarp();
-        if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward(a, m, s);
+        if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward<SS, MT>(a, m, s);
         __syncwarp();
     }
 }
@@ -398,9 +482,16 @@ bool mpc_slots_eligible(const MpcArgs& a, int* tpb_out) {
 }
 
 #ifndef B2C_HOST_EMUL
+template <int SS, int MT>
+static int slots_launch_t(b2c_ctx* ctx, const MpcArgs& a, int grid, size_t smem) {
+    B2C_CUDA(cudaFuncSetAttribute(k_mpc_slots<SS, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    k_mpc_slots<SS, MT><<<grid, SS, smem, ctx->stream>>>(a);
+    B2C_CHECK_LAUNCH(ctx);
+    return 0;
+}
+
 int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     const size_t smem = (size_t)slot_fields(a) * tpb * sizeof(double);
-    B2C_CUDA(cudaFuncSetAttribute(k_mpc_slots, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     int grid = (int)((a.B + tpb - 1) / tpb);
     if (grid > ctx->sm_count) grid = ctx->sm_count;
     a.nslots = (int64_t)grid * tpb;
@@ -411,14 +502,30 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     a.scratch = (double*)ctx->scratch;
     a.queue = (unsigned long long*)((char*)ctx->scratch + strip);
     B2C_CUDA(cudaMemsetAsync(a.queue, 0, sizeof(unsigned long long), ctx->stream));
-    k_mpc_slots<<<grid, tpb, smem, ctx->stream>>>(a);
-    B2C_CHECK_LAUNCH(ctx);
-    return 0;
+    // obstacle rows unrolled at compile time for the two shapes the reference runs (M = 3, 5)
+    if (tpb == 128) {
+        if (a.M == 5) return slots_launch_t<128, 5>(ctx, a, grid, smem);
+        if (a.M == 3) return slots_launch_t<128, 3>(ctx, a, grid, smem);
+        if (a.M == 0) return slots_launch_t<128, 0>(ctx, a, grid, smem);
+        return slots_launch_t<128, -1>(ctx, a, grid, smem);
+    }
+    if (tpb == 64) return slots_launch_t<64, -1>(ctx, a, grid, smem);
+    return slots_launch_t<32, -1>(ctx, a, grid, smem);
 }
 #else
 int mpc_slots_launch(b2c_ctx*, MpcArgs&, int) { return -1; }
 
 #include <vector>
+template <int MT>
+static void emul_one(const MpcArgs& a, const SlotMem& m, int64_t i) {
+    constexpr int SS = 1;
+    SlotState s;
+    slot_setup<SS, MT>(a, m, s, i);
+    while (s.mode != SLOT_IDLE) {
+        if (s.mode == SLOT_BWD) slot_phase_backward<SS, MT>(a, m, s);
+        if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward<SS, MT>(a, m, s);
+    }
+}
 // Test-only: the slot state machine on the host, one instance at a time (SoA host pointers).
 extern "C" int b2c_emul_mpc_slots(int64_t B, const b2c_mpc_params* p,
                                   const double* x0, const double* xref, const double* uref, const double* obs,
@@ -430,15 +537,13 @@ extern "C" int b2c_emul_mpc_slots(int64_t B, const b2c_mpc_params* p,
     if (!mpc_slots_eligible(a, &tpb)) return -5;
     std::vector<double> sm((size_t)slot_fields(a)), gl((size_t)14 * a.N);
     SlotMem m;
-    m.ss = 1; m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
+    m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
     m.gs = 1; m.g = gl.data(); m.gg = m.g + 6 * a.N;
     for (int64_t i = 0; i < B; ++i) {
-        SlotState s;
-        slot_setup(a, m, s, i);
-        while (s.mode != SLOT_IDLE) {
-            if (s.mode == SLOT_BWD) slot_phase_backward(a, m, s);
-            if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward(a, m, s);
-        }
+        if (a.M == 5) emul_one<5>(a, m, i);
+        else if (a.M == 3) emul_one<3>(a, m, i);
+        else if (a.M == 0) emul_one<0>(a, m, i);
+        else emul_one<-1>(a, m, i);
     }
     return 0;
 }
