@@ -24,6 +24,7 @@ namespace {
 
 struct SlotMem {
     double* w;  double* u;  double* ob;               // shared strips, element (f) at f*SS (host emulation: SS = 1)
+    double* ring;                                     // this lane's cell of ring slot 0 (device only)
     double* g;  double* gg; int64_t gs;               // global strips: stage k of this slot at g + k*6*gs / gg + k*8*gs
 };
 // 16-byte vector access to the global strips (6 resp. 8 contiguous doubles per stage and slot)
@@ -51,6 +52,41 @@ B2C_HD void gg_store(const SlotMem& m, int j, double K00, double K01, double K02
 #define MW(f)  m.w[(f) * SS]
 #define MU(f)  m.u[(f) * SS]
 #define MO(f)  m.ob[(f) * SS]
+
+// Two-stage ring in shared memory for the read-only stage constants: stage k+2 is fetched with
+// cp.async (LDGSTS, no register dependency) while stages k and k+1 are being computed, so the L2
+// latency of the G strip never reaches the recursion.  Cell of lane l, ring slot r: ring[(r*SS + l)*6 .. +6).
+// `dep` is a value computed from the cell being overwritten: it orders the refill after the read.
+template <int SS>
+B2C_HD void ring_issue(const SlotMem& m, int k, bool valid, double dep) {
+#ifdef __CUDA_ARCH__
+    if (valid) {
+        const double* src = m.g + (int64_t)k * 6 * m.gs;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(m.ring + (size_t)(k & 1) * 6 * SS);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\t"
+                     "cp.async.cg.shared.global [%0+16], [%1+16], 16;\n\t"
+                     "cp.async.cg.shared.global [%0+32], [%1+32], 16;  // after %2"
+                     :: "r"(dst), "l"(src), "d"(dep) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#else
+    (void)m; (void)k; (void)valid; (void)dep;
+#endif
+}
+template <int SS>
+B2C_HD Stage6 ring_take(const SlotMem& m, int k) {
+#ifdef __CUDA_ARCH__
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    const double2* p = reinterpret_cast<const double2*>(m.ring + (size_t)(k & 1) * 6 * SS);
+    const double2 a = p[0], b = p[1], c = p[2];
+    return Stage6{a.x, a.y, b.x, b.y, c.x, c.y};
+#else
+    return g_load(m, k);
+#endif
+}
+
+// shared-memory doubles per slot: strips W, U, OB (+ 12 for the two ring cells)
+__host__ __device__ static inline int slot_fields(const MpcArgs& a) { return 10 * a.N + 3 * a.M; }
 
 enum { SLOT_IDLE = 0, SLOT_BWD = 1, SLOT_FWD_GAIN = 2, SLOT_FWD_PLAIN = 3 };
 
@@ -139,11 +175,12 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
     double ox = zx, oy = zy, ot = zt;                 // old trajectory
     double J = 0.0, mv = 0.0;
     const double alpha = gain ? s.alpha : 0.0;
-    Stage6 cur = g_load(m, 0), nxt = g_load(m, (N > 1) ? 1 : 0);
+    ring_issue<SS>(m, 0, true, 0.0);
+    ring_issue<SS>(m, 1, N > 1, 0.0);
     for (int k = 0; k < N; ++k) {
-        // prefetch the constants two stages ahead (L2 latency hides behind two stages of arithmetic)
-        const Stage6 nn = g_load(m, (k + 2 < N) ? (k + 2) : (N - 1));
+        const Stage6 cur = ring_take<SS>(m, k);
         const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1, prx = cur.prx, pry = cur.pry;
+        ring_issue<SS>(m, k + 2, k + 2 < N, ck + pry);       // constants two stages ahead
         const double wo0 = MW(2 * k), wo1 = MW(2 * k + 1);
         double w0 = wo0, w1 = wo1;
         if (gain) {
@@ -167,14 +204,15 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
                 const double q = d2 + ddx * zx + ddy * zy;
                 if ((d2 > 1e-4) && (OCC[mm] * d2 > q * fabs(q))) hit |= (1u << mm);
             }
-            if (hit) {
-#pragma unroll
-                for (int mm = 0; mm < MR; ++mm) {
-                    if (hit & (1u << mm)) {
-                        const double ddx = prx - OX[mm], ddy = pry - OY[mm];
-                        slot_row(a, ddx, ddy, ddx * ddx + ddy * ddy, OC[mm], zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
-                    }
-                }
+            while (hit) {                                 // rare; lanes with different rows share an iteration
+#ifdef __CUDA_ARCH__
+                const int mm = __ffs(hit) - 1;
+#else
+                int mm = 0; while (!((hit >> mm) & 1u)) ++mm;
+#endif
+                hit &= hit - 1u;
+                const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1);
+                slot_row(a, ddx, ddy, ddx * ddx + ddy * ddy, MO(3 * mm + 2), zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
             }
         } else if (MT < 0) {
             for (int mm = 0; mm < M; ++mm) {
@@ -196,7 +234,6 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const SlotState& 
         const double nox = ox + a_k * ot + ck * wo0, noy = oy + b_k * ot + sk * wo0;
         zt = zt + a.dt * w1; zx = nzx; zy = nzy;
         ot = ot + a.dt * wo1; ox = nox; oy = noy;
-        cur = nxt; nxt = nn;
     }
     J += a.p0 * zx * zx + a.p1 * zy * zy + a.p2 * zt * zt;                       // terminal cost, :412
     lamx = a.p0 * zx; lamy = a.p1 * zy; lamt = a.p2 * zt;
@@ -216,12 +253,12 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     double v0 = s.lamx, v1 = s.lamy, v2 = s.lamt;     // value-function gradient
     double l0 = v0, l1 = v1, l2 = v2;                 // true costate
     double dec = 0.0;
-    double ck, sk, uo0, uo1, nck, nsk, nuo0, nuo1;
-    g_load4(m, N - 1, ck, sk, uo0, uo1);
-    g_load4(m, (N > 1) ? (N - 2) : 0, nck, nsk, nuo0, nuo1);
+    ring_issue<SS>(m, N - 1, true, 0.0);
+    ring_issue<SS>(m, N - 2, N > 1, 0.0);
     for (int j = N - 1; j >= 0; --j) {
-        double pck, psk, puo0, puo1;                  // two stages ahead
-        g_load4(m, (j > 1) ? (j - 2) : 0, pck, psk, puo0, puo1);
+        const Stage6 cur = ring_take<SS>(m, j);
+        const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1;
+        ring_issue<SS>(m, j - 2, j >= 2, ck + cur.pry);      // constants two stages ahead
         const double gz0 = MU(8 * j + 0), gz1 = MU(8 * j + 1), gz2 = MU(8 * j + 2);
         const double H0 = MU(8 * j + 3), H1 = MU(8 * j + 4), H3 = MU(8 * j + 5);
         const double w0 = MW(2 * j), w1 = MW(2 * j + 1);
@@ -274,8 +311,6 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         v0 = qz0 - (U00 * k0 + U10 * k1);
         v1 = qz1 - (U01 * k0 + U11 * k1);
         v2 = qz2 - (U02 * k0 + U12 * k1);
-        ck = nck; sk = nsk; uo0 = nuo0; uo1 = nuo1;
-        nck = pck; nsk = psk; nuo0 = puo0; nuo1 = puo1;
     }
     return dec;
 }
@@ -289,7 +324,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
 template <int SS, int MT>
 B2C_HD void slot_restore(const MpcArgs& a, const SlotMem& m, const bool open_loop) {
     const int N = a.N;
-#pragma unroll 2
+#pragma unroll 4
     for (int j = 0; j < N; ++j) {
         MW(2 * j) = MU(8 * j + 6); MW(2 * j + 1) = MU(8 * j + 7);
         const double2* p = reinterpret_cast<const double2*>(m.gg + (int64_t)j * 8 * m.gs);
@@ -434,6 +469,7 @@ k_mpc_slots(const MpcArgs a) {
     m.w = smem + threadIdx.x;
     m.u = m.w + (size_t)2 * a.N * tpb;
     m.ob = m.u + (size_t)8 * a.N * tpb;
+    m.ring = smem + (size_t)slot_fields(a) * tpb + (size_t)threadIdx.x * 6;
     m.gs = a.nslots;
     m.g = a.scratch + slot * 6;
     m.gg = a.scratch + (int64_t)6 * a.N * a.nslots + slot * 8;
@@ -469,14 +505,12 @@ k_mpc_slots(const MpcArgs a) {
 
 }  // namespace
 
-// shared-memory doubles per slot
-static inline int slot_fields(const MpcArgs& a) { return 10 * a.N + 3 * a.M; }
 
 bool mpc_slots_eligible(const MpcArgs& a, int* tpb_out) {
     if (a.kind != B2C_MPC_LTV || a.bs != 1 || !a.soft) return false;
     const size_t cap = 227 * 1024;
     for (int tpb = 128; tpb >= 32; tpb >>= 1) {
-        if ((size_t)slot_fields(a) * tpb * sizeof(double) <= cap) { *tpb_out = tpb; return true; }
+        if ((size_t)(slot_fields(a) + 12) * tpb * sizeof(double) <= cap) { *tpb_out = tpb; return true; }
     }
     return false;
 }
@@ -491,7 +525,7 @@ static int slots_launch_t(b2c_ctx* ctx, const MpcArgs& a, int grid, size_t smem)
 }
 
 int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
-    const size_t smem = (size_t)slot_fields(a) * tpb * sizeof(double);
+    const size_t smem = (size_t)(slot_fields(a) + 12) * tpb * sizeof(double);
     int grid = (int)((a.B + tpb - 1) / tpb);
     if (grid > ctx->sm_count) grid = ctx->sm_count;
     a.nslots = (int64_t)grid * tpb;
@@ -537,7 +571,7 @@ extern "C" int b2c_emul_mpc_slots(int64_t B, const b2c_mpc_params* p,
     if (!mpc_slots_eligible(a, &tpb)) return -5;
     std::vector<double> sm((size_t)slot_fields(a)), gl((size_t)14 * a.N);
     SlotMem m;
-    m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
+    m.ring = nullptr; m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
     m.gs = 1; m.g = gl.data(); m.gg = m.g + 6 * a.N;
     for (int64_t i = 0; i < B; ++i) {
         if (a.M == 5) emul_one<5>(a, m, i);
