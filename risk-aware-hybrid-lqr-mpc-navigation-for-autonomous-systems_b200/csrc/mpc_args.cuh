@@ -20,6 +20,8 @@ struct MpcArgs {
     // slot kernel only
     unsigned long long* queue;   // next unclaimed instance index
     int64_t nslots;              // resident slots (= grid * block)
+    unsigned long long* class_count;   // instances per difficulty class (claim order), or unused
+    uint32_t* perm;              // [class][B] instance ids in claim order; NULL = claim in index order
 };
 
 // np.unwrap step (numpy/lib/function_base.py semantics, period 2pi, discont pi)
@@ -49,7 +51,7 @@ static inline void mpc_fill_args(MpcArgs& a, int64_t B, const b2c_mpc_params* p,
     a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
     a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
     a.useq = useq; a.xpred = xpred;
-    a.scratch = nullptr; a.queue = nullptr; a.nslots = 0;
+    a.scratch = nullptr; a.queue = nullptr; a.nslots = 0; a.class_count = nullptr; a.perm = nullptr;
 }
 
 // mpc_slots.cu

@@ -456,8 +456,66 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
     }
 }
 
+// ----- difficulty classes (work ordering only; never changes a result) ------------------------------
+// The Newton iteration count of an instance is predicted well by how deep its REFERENCE path runs into
+// an inflated obstacle: margin = min_{k<N, m} (|p_ref,k - p_obs,m| - (d_safe + r_m)).  On config 4:
+// margin < -0.1 m -> 4.7 iterations on average (max 13), [-0.1, 0) -> 2.9, [0, 0.1) -> 1.7, >= 0.1 -> 1.26
+// (max 5).  The persistent kernel claims the hard classes first (longest-processing-time-first), which
+// removes the tail a first-come queue leaves when the last instances claimed happen to be slow ones, and
+// keeps warps homogeneous (lanes of a warp finish, and refill, together).
+#define MPC_NCLASS 4
+B2C_HD int mpc_difficulty_class(const MpcArgs& a, int64_t i) {
+    const int64_t B = a.B;
+    int cls = MPC_NCLASS - 1;
+    for (int m = 0; m < a.M; ++m) {
+        const double ox = B2C_LDG(a.obs + (int64_t)(3 * m) * B + i), oy = B2C_LDG(a.obs + (int64_t)(3 * m + 1) * B + i);
+        const double c = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * m + 2) * B + i);
+        const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
+        const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
+        double d2min = 1e300;
+        for (int k = 0; k < a.N; ++k) {
+            const double dx = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i) - ox;
+            const double dy = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i) - oy;
+            d2min = fmin(d2min, dx * dx + dy * dy);
+        }
+        const int cm_ = (d2min < t0) ? 0 : (d2min < t1) ? 1 : (d2min < t2) ? 2 : 3;
+        cls = (cm_ < cls) ? cm_ : cls;
+    }
+    return cls;
+}
+
+#ifndef B2C_HOST_EMUL
+// perm[c*B + pos] = instance ids of class c in arrival order (warp-aggregated counters: a warp's 32
+// consecutive instances stay contiguous inside each class, so refills still read coalesced rows).
+__global__ void __launch_bounds__(128)
+k_mpc_classify(const MpcArgs a) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int cls = (i < a.B) ? mpc_difficulty_class(a, i) : -1;
+#pragma unroll
+    for (int c = 0; c < MPC_NCLASS; ++c) {
+        const unsigned mask = __ballot_sync(0xffffffffu, cls == c);
+        if (!mask) continue;
+        const int leader = __ffs(mask) - 1;
+        unsigned long long base = 0;
+        if (lane == leader) base = atomicAdd(a.class_count + c, (unsigned long long)__popc(mask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (cls == c) a.perm[(int64_t)c * a.B + (int64_t)base + __popc(mask & ((1u << lane) - 1u))] = (uint32_t)i;
+    }
+}
+#endif
+
 // ----- kernel ---------------------------------------------------------------------------------------
 #ifndef B2C_HOST_EMUL
+#ifdef B2C_SLOT_TRACE                                 // tools/ only (make trace): per-warp phase timing
+__device__ unsigned long long g_slot_trace[8 * 4096];
+__device__ __forceinline__ unsigned long long trace_ns() {
+    unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
+}
+#define TRACE(...) __VA_ARGS__
+#else
+#define TRACE(...)
+#endif
 template <int SS, int MT>
 __global__ void __launch_bounds__(SS, 1)
 k_mpc_slots(const MpcArgs a) {
@@ -479,9 +537,14 @@ k_mpc_slots(const MpcArgs a) {
     s.x0x = s.x0t = s.r0x = s.r0t = 0.0;
     bool empty = false;
     const unsigned FULL = 0xffffffffu;
+    unsigned long long cum0 = 0, cum1 = 0, cum2 = 0;          // class boundaries in queue order
+    if (a.perm) { cum0 = a.class_count[0]; cum1 = cum0 + a.class_count[1]; cum2 = cum1 + a.class_count[2]; }
+    TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;)
     for (;;) {
+        TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE));)
         if (s.mode == SLOT_BWD) slot_phase_backward<SS, MT>(a, m, s);
         __syncwarp();
+        TRACE(tr_b += clock64() - tr_c; tr_c = clock64();)
         const bool want = (s.mode == SLOT_IDLE) && !empty;
         const unsigned need = __ballot_sync(FULL, want);
         if (need) {
@@ -490,16 +553,33 @@ k_mpc_slots(const MpcArgs a) {
             if (lane == leader) base = atomicAdd(a.queue, (unsigned long long)__popc(need));
             base = __shfl_sync(FULL, base, leader);
             if (want) {
-                const int64_t id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
-                if (id < a.B) slot_setup<SS, MT>(a, m, s, id);
+                int64_t id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                if (id < a.B) {
+                    if (a.perm) {                             // queue position -> (class, offset) -> instance
+                        const unsigned long long q = (unsigned long long)id;
+                        const int c = (q >= cum0) + (q >= cum1) + (q >= cum2);
+                        const unsigned long long lo = (c == 0) ? 0ull : (c == 1) ? cum0 : (c == 2) ? cum1 : cum2;
+                        id = (int64_t)a.perm[(int64_t)c * a.B + (int64_t)(q - lo)];
+                    }
+                    slot_setup<SS, MT>(a, m, s, id);
+                }
             }
             if ((int64_t)base + __popc(need) >= a.B) empty = true;
         }
         if (empty && __all_sync(FULL, s.mode == SLOT_IDLE)) break;
         __syncwarp();
+        TRACE(tr_r += clock64() - tr_c; tr_c = clock64();)
         if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward<SS, MT>(a, m, s);
         __syncwarp();
+        TRACE(tr_f += clock64() - tr_c;)
     }
+    TRACE(if (lane == 0) {
+        const int w = (blockIdx.x * SS + threadIdx.x) >> 5;
+        if (w < 4096) {
+            unsigned long long* t = g_slot_trace + 8 * w;
+            t[0] = tr_t0; t[1] = trace_ns(); t[2] = tr_rounds; t[3] = tr_b; t[4] = tr_r; t[5] = tr_f; t[6] = tr_lanes; t[7] = 1;
+        }
+    })
 }
 #endif
 
@@ -531,11 +611,21 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     a.nslots = (int64_t)grid * tpb;
     // global strips: G[6N] + GG[8N] doubles per slot, then the queue counter
     const size_t strip = (size_t)(14 * a.N) * (size_t)a.nslots * sizeof(double);
-    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, strip + 256, false);
+    // more than one instance per slot: claim in difficulty order (see mpc_difficulty_class)
+    const bool ordered = a.M > 0 && a.B > a.nslots && a.B < ((int64_t)1 << 32);
+    const size_t perm_bytes = ordered ? (size_t)MPC_NCLASS * (size_t)a.B * sizeof(uint32_t) : 0;
+    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, strip + 256 + perm_bytes, false);
     if (rc) return rc;
     a.scratch = (double*)ctx->scratch;
     a.queue = (unsigned long long*)((char*)ctx->scratch + strip);
-    B2C_CUDA(cudaMemsetAsync(a.queue, 0, sizeof(unsigned long long), ctx->stream));
+    a.class_count = a.queue + 1;
+    a.perm = nullptr;
+    B2C_CUDA(cudaMemsetAsync(a.queue, 0, (1 + MPC_NCLASS) * sizeof(unsigned long long), ctx->stream));
+    if (ordered) {
+        a.perm = (uint32_t*)((char*)ctx->scratch + strip + 256);
+        k_mpc_classify<<<b2c_blocks(a.B, 128), 128, 0, ctx->stream>>>(a);
+        B2C_CHECK_LAUNCH(ctx);
+    }
     // obstacle rows unrolled at compile time for the two shapes the reference runs (M = 3, 5)
     if (tpb == 128) {
         if (a.M == 5) return slots_launch_t<128, 5>(ctx, a, grid, smem);
@@ -546,6 +636,12 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     if (tpb == 64) return slots_launch_t<64, -1>(ctx, a, grid, smem);
     return slots_launch_t<32, -1>(ctx, a, grid, smem);
 }
+#ifdef B2C_SLOT_TRACE
+extern "C" int b2c_debug_slot_trace(unsigned long long* out, int nwarps) {
+    B2C_CUDA(cudaMemcpyFromSymbol(out, g_slot_trace, (size_t)nwarps * 8 * sizeof(unsigned long long)));
+    return 0;
+}
+#endif
 #else
 int mpc_slots_launch(b2c_ctx*, MpcArgs&, int) { return -1; }
 

@@ -10,7 +10,8 @@ import threading
 
 import numpy as np
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb2c.so")
+# B2C_LIB: developer override (instrumented builds under tools/); always a CUDA build of the same ABI
+LIB_PATH = os.environ.get("B2C_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb2c.so")
 
 LIN_JACOBIAN, LIN_EULER, LIN_EXACT = 0, 1, 2
 GUARD_NONE, GUARD_LQR, GUARD_MPC = 0, 1, 2

@@ -1,0 +1,67 @@
+#!/usr/bin/env python3
+"""Per-warp phase timing of k_mpc_slots (instrumented build: `make -C <pkg>/csrc trace`).
+
+    B2C_LIB=tools/_trace/libb2c_trace.so python tools/slot_trace.py [--B 65536]
+Prints, for one launch: when warps finish relative to the first start, rounds per warp, cycles per round in
+the backward / refill (finish + setup) / forward phases, and the mean number of busy lanes per round."""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+os.environ.setdefault("B2C_LIB", os.path.join(ROOT, "tools", "_trace", "libb2c_trace.so"))
+sys.path.insert(0, os.path.join(ROOT, "risk-aware-hybrid-lqr-mpc-navigation-for-autonomous-systems_b200"))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+from hybrid_controller import _native as nat, workloads as wl  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--B", type=int, default=65536)
+    ap.add_argument("--seed", type=int, default=0)
+    args = ap.parse_args()
+    B, N = args.B, 20
+    dev = torch.device("cuda", 0)
+    ctx = nat.Context(0)
+    reps = -(-B // 65536)
+    arrs = [np.concatenate([wl.config4_instances(65536, N=N, seed=args.seed + s)[j] for s in range(reps)])[:B]
+            for j in range(4)]
+    d = [torch.from_numpy(np.ascontiguousarray(a.reshape(B, -1))).to(dev).t().contiguous() for a in arrs]
+    u0 = torch.empty((2, B), dtype=torch.float64, device=dev)
+    cost = torch.empty(B, dtype=torch.float64, device=dev)
+    st, it, sl = (torch.empty(B, dtype=torch.int32, device=dev) for _ in range(3))
+    prm = nat.mpc_params(nat.MPC_LTV, N, 5, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02, engine=2)
+    for _ in range(4):
+        ctx.call("b2c_mpc_dev", B, C.byref(prm), d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), d[3].data_ptr(),
+                 None, u0.data_ptr(), cost.data_ptr(), st.data_ptr(), it.data_ptr(), sl.data_ptr(), None, None)
+        ctx.sync()
+    nw = min(4096, 148 * 4)
+    buf = (C.c_ulonglong * (8 * nw))()
+    f = ctx.lib.b2c_debug_slot_trace
+    f.argtypes = [C.c_void_p, C.c_int]
+    assert f(buf, nw) == 0
+    t = np.frombuffer(buf, dtype=np.uint64).reshape(nw, 8).astype(np.float64)
+    t = t[t[:, 7] == 1]
+    t0 = t[:, 0].min()
+    end = (t[:, 1] - t0) / 1e3
+    rounds = t[:, 2]
+    cyc = t[:, 3:6]
+    q = lambda a: [float(np.percentile(a, p)) for p in (0, 10, 50, 90, 100)]
+    print(json.dumps({
+        "B": B, "warps": len(t), "iters_mean": float(it.float().mean()), "iters_max": int(it.max()),
+        "start_spread_us": float((t[:, 0].max() - t0) / 1e3),
+        "warp_end_us_pct_0_10_50_90_100": q(end),
+        "rounds_per_warp_pct": q(rounds),
+        "busy_lanes_per_round": float(t[:, 6].sum() / rounds.sum()),
+        "cycles_per_round": {"backward": float(cyc[:, 0].sum() / rounds.sum()),
+                             "refill": float(cyc[:, 1].sum() / rounds.sum()),
+                             "forward": float(cyc[:, 2].sum() / rounds.sum())},
+        "us_per_round_mean": float(((t[:, 1] - t[:, 0]) / 1e3).sum() / rounds.sum()),
+    }))
+
+
+if __name__ == "__main__":
+    main()
