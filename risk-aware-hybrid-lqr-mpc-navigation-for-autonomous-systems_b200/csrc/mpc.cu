@@ -390,7 +390,8 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
             if (!(dec < 1e300)) { st = B2C_NONFINITE; break; }
             if (dec <= a.tol * fmax(1.0, fabs(J))) { st = B2C_OK; break; }
             if (it >= a.max_iter) { st = B2C_MAXITER; break; }
-            ++it; alpha = 1.0; ls = 0; need_backward = false;
+            alpha = (it == 0) ? 1.0 : fmin(1.0, MPC_LS_GROW * alpha);
+            ++it; ls = 0; need_backward = false;
         }
         double tlx, tly, tlt, tviol;
         bool dummy = false;
@@ -400,7 +401,7 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
         } else {
             alpha *= 0.5;
             ++ls;
-            if (ls == MPC_LS_CLOSED) { mpc_gains_to_open_loop<BS1>(a, i); alpha = 1.0; }
+            if (ls == MPC_LS_CLOSED) mpc_gains_to_open_loop<BS1>(a, i);     // the arc continues from this alpha
             if (ls >= MPC_LS_MAX) {               // cannot decrease any further: rounding floor or stall
                 st = (dec <= 1e-9 * fmax(1.0, fabs(J))) ? B2C_OK : B2C_MAXITER;
                 break;

@@ -428,7 +428,8 @@ B2C_HD void slot_phase_backward(const MpcArgs& a, const SlotMem& m, SlotState& s
     if (!(s.dec < 1e300)) { s.st = B2C_NONFINITE; slot_finish<SS, MT>(a, m, s); return; }
     if (s.dec <= a.tol * fmax(1.0, fabs(s.J))) { s.st = B2C_OK; slot_finish<SS, MT>(a, m, s); return; }
     if (s.it >= a.max_iter) { s.st = B2C_MAXITER; slot_finish<SS, MT>(a, m, s); return; }
-    ++s.it; s.alpha = 1.0; s.ls = 0; s.mode = SLOT_FWD_GAIN;
+    s.alpha = (s.it == 0) ? 1.0 : fmin(1.0, MPC_LS_GROW * s.alpha);     // first trial: see mpc_args.cuh
+    ++s.it; s.ls = 0; s.mode = SLOT_FWD_GAIN;
 }
 
 template <int SS, int MT>
@@ -447,8 +448,7 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
         s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt; s.mode = SLOT_BWD;
         return;
     }
-    s.alpha *= 0.5; ++s.ls;                       // reject: undo, shorten
-    if (s.ls == MPC_LS_CLOSED) s.alpha = 1.0;
+    s.alpha *= 0.5; ++s.ls;                       // reject: undo, shorten (the arc continues from this alpha)
     slot_restore<SS, MT>(a, m, s.ls >= MPC_LS_CLOSED);
     if (s.ls >= MPC_LS_MAX) {                     // rounding floor or stall
         s.st = (s.dec <= 1e-9 * fmax(1.0, fabs(s.J))) ? B2C_OK : B2C_MAXITER;
