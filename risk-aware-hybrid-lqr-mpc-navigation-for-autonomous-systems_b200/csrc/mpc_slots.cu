@@ -95,27 +95,52 @@ struct SlotState {
     int mode, it, ls, st;
     double alpha, J, dec, z0x, z0y, z0t, lamx, lamy, lamt, max_viol;
     double x0x, x0t, r0x, r0t;                        // kept for the fallback law
+    double ur00, ur01;                                // first reference input (outputs)
 };
 
 // ----- setup: claim instance i, stage its constants, w = clip(0) ---------------------------------
-// Two passes so that the instance's input loads (HBM, partially coalesced: lanes that refill in the
-// same round hold consecutive instance ids) are all in flight together: pass 1 copies the raw rows
-// into the (still unused) U strip, pass 2 does the unwrap / sincos arithmetic from shared memory.
+// Three steps so that a warp can share the work of the lanes that refill in a round (kernel: the
+// (lane, stage) pairs of steps 1 and 3 are dealt out over all 32 lanes; host emulation: plain loops):
+//   1. setup_load_stage : raw rows of stage k (theta_ref, u_ref, p_ref) -> the (still unused) U strip
+//   2. setup_owner      : x0 / first reference row / obstacles, np.unwrap along the horizon (sequential,
+//                         cheap: one compare per stage unless the heading crosses +-pi)
+//   3. setup_stage      : sincos of the unwrapped heading -> G strip, w_k = clip(0) -> W strip
+template <int SS>
+B2C_HD void setup_load_stage(const MpcArgs& a, const SlotMem& m, int64_t i, int k) {
+    const int64_t B = a.B;
+    MU(8 * k + 0) = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
+    MU(8 * k + 1) = B2C_LDG(a.uref + (int64_t)(2 * k) * B + i);
+    MU(8 * k + 2) = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * B + i);
+    MU(8 * k + 3) = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
+    MU(8 * k + 4) = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+}
+
+#ifndef B2C_HOST_EMUL
+// the same five rows with cp.async (global -> shared without a register round trip): a warp puts the rows
+// of every refilling lane in flight at once and waits for all of them together
+template <int SS>
+__device__ __forceinline__ void setup_load_stage_async(const MpcArgs& a, const SlotMem& m, int64_t i, int k) {
+#ifdef __CUDA_ARCH__
+    const int64_t B = a.B;
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(&MU(8 * k));
+    const double* xr = a.xref + (int64_t)(3 * k) * B + i;
+    const double* ur = a.uref + (int64_t)(2 * k) * B + i;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst), "l"(xr + 2 * B) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst + 1 * SS * 8), "l"(ur) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst + 2 * SS * 8), "l"(ur + B) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst + 3 * SS * 8), "l"(xr) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst + 4 * SS * 8), "l"(xr + B) : "memory");
+#endif
+}
+#endif
+
 template <int SS, int MT>
-B2C_HD void slot_setup(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
+B2C_HD void setup_owner(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
     const int N = a.N, M = (MT >= 0) ? MT : a.M;
     const int64_t B = a.B;
     s.inst = i; s.it = 0; s.ls = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
     const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + B + i), x0t = B2C_LDG(a.x0 + 2 * B + i);
     const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + B + i), r0t = B2C_LDG(a.xref + 2 * B + i);
-#pragma unroll 4
-    for (int k = 0; k < N; ++k) {
-        MU(8 * k + 0) = B2C_LDG(a.xref + (int64_t)(3 * k + 2) * B + i);
-        MU(8 * k + 1) = B2C_LDG(a.uref + (int64_t)(2 * k) * B + i);
-        MU(8 * k + 2) = B2C_LDG(a.uref + (int64_t)(2 * k + 1) * B + i);
-        MU(8 * k + 3) = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i);
-        MU(8 * k + 4) = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
-    }
     for (int e = 0; e < M; ++e) {                 // obstacle strip: x, y, d_safe + r
         MO(3 * e)     = B2C_LDG(a.obs + (int64_t)(3 * e) * B + i);
         MO(3 * e + 1) = B2C_LDG(a.obs + (int64_t)(3 * e + 1) * B + i);
@@ -123,17 +148,40 @@ B2C_HD void slot_setup(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t
     }
     s.x0x = x0x; s.x0t = x0t; s.r0x = r0x; s.r0t = r0t;
     s.z0x = x0x - r0x; s.z0y = x0y - r0y; s.z0t = b2c_wrap(x0t - r0t);       // :392-401, :421
-    double th_prev = r0t, cum = 0.0;                                          // np.unwrap along the horizon
-    for (int k = 0; k < N; ++k) {
-        const double th_raw = MU(8 * k + 0), uo0 = MU(8 * k + 1), uo1 = MU(8 * k + 2);
-        if (k > 0) cum += unwrap_correction(th_raw - th_prev);
-        th_prev = th_raw;
-        double sn, cs; sincos(th_raw + cum, &sn, &cs);
-        g_store(m, k, cs * a.dt, sn * a.dt, uo0, uo1, MU(8 * k + 3), MU(8 * k + 4));
-        MW(2 * k)     = b2c_clip(0.0, -a.v_max - uo0, a.v_max - uo0);
-        MW(2 * k + 1) = b2c_clip(0.0, -a.w_max - uo1, a.w_max - uo1);
-    }
     s.mode = SLOT_FWD_PLAIN;
+}
+
+// np.unwrap along the horizon, in place on the staged headings (after the stage rows have landed)
+template <int SS>
+B2C_HD void setup_unwrap(const MpcArgs& a, const SlotMem& m, SlotState& s, const bool any_jump) {
+    const int N = a.N;
+    s.ur00 = MU(1); s.ur01 = MU(2);
+    if (!any_jump) return;                            // every |step| < pi: np.unwrap is the identity
+    double th_prev = s.r0t, cum = 0.0;
+    for (int k = 1; k < N; ++k) {
+        const double th_raw = MU(8 * k + 0);
+        cum += unwrap_correction(th_raw - th_prev);
+        th_prev = th_raw;
+        if (cum != 0.0) MU(8 * k + 0) = th_raw + cum;
+    }
+}
+
+template <int SS>
+B2C_HD void setup_stage(const MpcArgs& a, const SlotMem& m, int k) {
+    const double th = MU(8 * k + 0), uo0 = MU(8 * k + 1), uo1 = MU(8 * k + 2);
+    double sn, cs; sincos(th, &sn, &cs);
+    g_store(m, k, cs * a.dt, sn * a.dt, uo0, uo1, MU(8 * k + 3), MU(8 * k + 4));
+    MW(2 * k)     = b2c_clip(0.0, -a.v_max - uo0, a.v_max - uo0);
+    MW(2 * k + 1) = b2c_clip(0.0, -a.w_max - uo1, a.w_max - uo1);
+}
+
+// the three steps for one lane on its own (host emulation, and the reference order of operations)
+template <int SS, int MT>
+B2C_HD void slot_setup(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
+    for (int k = 0; k < a.N; ++k) setup_load_stage<SS>(a, m, i, k);
+    setup_owner<SS, MT>(a, m, s, i);
+    setup_unwrap<SS>(a, m, s, true);
+    for (int k = 0; k < a.N; ++k) setup_stage<SS>(a, m, k);
 }
 
 // one soft obstacle row, exact arithmetic (:439-468): accumulates cost / gradient / Hessian if violated
@@ -358,8 +406,7 @@ template <int SS, int MT>
 B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
     const int N = a.N;
     const int64_t B = a.B, i = s.inst;
-    const Stage6 g0 = g_load(m, 0);
-    const double ur00 = g0.uo0, ur01 = g0.uo1;
+    const double ur00 = s.ur00, ur01 = s.ur01;
     double u00, u01, Jout, mv = s.max_viol;
     const int sc = a.step_count ? a.step_count[i] : a.ramp_up_steps;
     if (s.st == B2C_OK) {
@@ -508,7 +555,7 @@ k_mpc_classify(const MpcArgs a) {
 // ----- kernel ---------------------------------------------------------------------------------------
 #ifndef B2C_HOST_EMUL
 #ifdef B2C_SLOT_TRACE                                 // tools/ only (make trace): per-warp phase timing
-__device__ unsigned long long g_slot_trace[8 * 4096];
+__device__ unsigned long long g_slot_trace[16 * 4096];
 __device__ __forceinline__ unsigned long long trace_ns() {
     unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
 }
@@ -534,12 +581,13 @@ k_mpc_slots(const MpcArgs a) {
     SlotState s;
     s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0;
     s.alpha = s.J = s.dec = s.z0x = s.z0y = s.z0t = s.lamx = s.lamy = s.lamt = s.max_viol = 0.0;
-    s.x0x = s.x0t = s.r0x = s.r0t = 0.0;
+    s.x0x = s.x0t = s.r0x = s.r0t = s.ur00 = s.ur01 = 0.0;
     bool empty = false;
     const unsigned FULL = 0xffffffffu;
     unsigned long long cum0 = 0, cum1 = 0, cum2 = 0;          // class boundaries in queue order
     if (a.perm) { cum0 = a.class_count[0]; cum1 = cum0 + a.class_count[1]; cum2 = cum1 + a.class_count[2]; }
-    TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;)
+    TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;
+          long long tr_x0 = 0, tr_x1 = 0, tr_x2 = 0, tr_x3 = 0, tr_x4 = 0, tr_x5 = 0;)
     for (;;) {
         TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE));)
         if (s.mode == SLOT_BWD) slot_phase_backward<SS, MT>(a, m, s);
@@ -552,17 +600,76 @@ k_mpc_slots(const MpcArgs a) {
             unsigned long long base = 0;
             if (lane == leader) base = atomicAdd(a.queue, (unsigned long long)__popc(need));
             base = __shfl_sync(FULL, base, leader);
+            int64_t id = 0;
+            bool id_ok = false;
             if (want) {
-                int64_t id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
                 if (id < a.B) {
+                    id_ok = true;
                     if (a.perm) {                             // queue position -> (class, offset) -> instance
                         const unsigned long long q = (unsigned long long)id;
                         const int c = (q >= cum0) + (q >= cum1) + (q >= cum2);
                         const unsigned long long lo = (c == 0) ? 0ull : (c == 1) ? cum0 : (c == 2) ? cum1 : cum2;
                         id = (int64_t)a.perm[(int64_t)c * a.B + (int64_t)(q - lo)];
                     }
-                    slot_setup<SS, MT>(a, m, s, id);
                 }
+            }
+            const bool fresh = want && id_ok;
+            TRACE(tr_x0 += clock64() - tr_c; long long tr_c2 = clock64();)
+            // the refilling lanes' setup, shared by the whole warp: task t = (stage k, refilling lane n),
+            // n fastest so that neighbouring tasks read neighbouring instances of the same input row.
+            // (k, n) advance by (32 / cnt, 32 % cnt) per pass; lane r holds the r-th refilling lane's number.
+            const unsigned vmask = __ballot_sync(FULL, fresh);
+            const int cnt = __popc(vmask), T = cnt * a.N;
+            if (cnt) {
+                const int nth = __fns(vmask, 0, (lane < cnt ? lane : 0) + 1);
+                const int dk = 32 / cnt, dn = 32 - dk * cnt;
+                int k = lane / cnt, n = lane - k * cnt;
+                for (int t = lane; t - lane < T; t += 32) {
+                    const int tl = __shfl_sync(FULL, nth, n);
+                    const int64_t tid = __shfl_sync(FULL, id, tl);
+                    if (t < T) {
+                        SlotMem tm = m;
+                        tm.w += tl - lane; tm.u += tl - lane;
+                        setup_load_stage_async<SS>(a, tm, tid, k);
+                    }
+                    k += dk; n += dn;
+                    if (n >= cnt) { n -= cnt; ++k; }
+                }
+                TRACE(tr_x4 += clock64() - tr_c2;)
+                if (fresh) setup_owner<SS, MT>(a, m, s, id);      // its loads overlap the rows in flight
+                TRACE(__syncwarp(); tr_x5 += clock64() - tr_c2;)
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                __syncwarp();
+                TRACE(tr_x1 += clock64() - tr_c2; tr_c2 = clock64();)
+                // np.unwrap: a warp-wide look for any heading step of pi or more; only then the sequential pass
+                bool jump = false;
+                k = lane / cnt; n = lane - k * cnt;
+                for (int t = lane; t - lane < T; t += 32) {
+                    const int tl = __shfl_sync(FULL, nth, n);
+                    if (t < T && k > 0) {
+                        const double* u = m.u + (tl - lane);
+                        jump |= !(fabs(u[(size_t)(8 * k) * SS] - u[(size_t)(8 * k - 8) * SS]) < 3.141592653589793);
+                    }
+                    k += dk; n += dn;
+                    if (n >= cnt) { n -= cnt; ++k; }
+                }
+                const bool any_jump = __any_sync(FULL, jump);
+                if (fresh) setup_unwrap<SS>(a, m, s, any_jump);
+                __syncwarp();
+                TRACE(tr_x2 += clock64() - tr_c2; tr_c2 = clock64();)
+                k = lane / cnt; n = lane - k * cnt;
+                for (int t = lane; t - lane < T; t += 32) {
+                    const int tl = __shfl_sync(FULL, nth, n);
+                    if (t < T) {
+                        SlotMem tm = m;
+                        tm.w += tl - lane; tm.u += tl - lane; tm.g += (int64_t)(tl - lane) * 6;
+                        setup_stage<SS>(a, tm, k);
+                    }
+                    k += dk; n += dn;
+                    if (n >= cnt) { n -= cnt; ++k; }
+                }
+                TRACE(__syncwarp(); tr_x3 += clock64() - tr_c2;)
             }
             if ((int64_t)base + __popc(need) >= a.B) empty = true;
         }
@@ -576,8 +683,9 @@ k_mpc_slots(const MpcArgs a) {
     TRACE(if (lane == 0) {
         const int w = (blockIdx.x * SS + threadIdx.x) >> 5;
         if (w < 4096) {
-            unsigned long long* t = g_slot_trace + 8 * w;
+            unsigned long long* t = g_slot_trace + 16 * w;
             t[0] = tr_t0; t[1] = trace_ns(); t[2] = tr_rounds; t[3] = tr_b; t[4] = tr_r; t[5] = tr_f; t[6] = tr_lanes; t[7] = 1;
+            t[8] = tr_x0; t[9] = tr_x1; t[10] = tr_x2; t[11] = tr_x3; t[12] = tr_x4; t[13] = tr_x5;
         }
     })
 }
@@ -638,7 +746,7 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
 }
 #ifdef B2C_SLOT_TRACE
 extern "C" int b2c_debug_slot_trace(unsigned long long* out, int nwarps) {
-    B2C_CUDA(cudaMemcpyFromSymbol(out, g_slot_trace, (size_t)nwarps * 8 * sizeof(unsigned long long)));
+    B2C_CUDA(cudaMemcpyFromSymbol(out, g_slot_trace, (size_t)nwarps * 16 * sizeof(unsigned long long)));
     return 0;
 }
 #endif

@@ -39,11 +39,11 @@ def main():
                  None, u0.data_ptr(), cost.data_ptr(), st.data_ptr(), it.data_ptr(), sl.data_ptr(), None, None)
         ctx.sync()
     nw = min(4096, 148 * 4)
-    buf = (C.c_ulonglong * (8 * nw))()
+    buf = (C.c_ulonglong * (16 * nw))()
     f = ctx.lib.b2c_debug_slot_trace
     f.argtypes = [C.c_void_p, C.c_int]
     assert f(buf, nw) == 0
-    t = np.frombuffer(buf, dtype=np.uint64).reshape(nw, 8).astype(np.float64)
+    t = np.frombuffer(buf, dtype=np.uint64).reshape(nw, 16).astype(np.float64)
     t = t[t[:, 7] == 1]
     t0 = t[:, 0].min()
     end = (t[:, 1] - t0) / 1e3
@@ -59,6 +59,8 @@ def main():
         "cycles_per_round": {"backward": float(cyc[:, 0].sum() / rounds.sum()),
                              "refill": float(cyc[:, 1].sum() / rounds.sum()),
                              "forward": float(cyc[:, 2].sum() / rounds.sum())},
+        "refill_cycles_per_round": dict(zip(("claim", "rows_in_flight", "unwrap", "sincos_stage", "rows_issued_at", "owner_done_at"),
+                                            (t[:, 8:14].sum(axis=0) / rounds.sum()).tolist())),
         "us_per_round_mean": float(((t[:, 1] - t[:, 0]) / 1e3).sum() / rounds.sum()),
     }))
 
