@@ -301,9 +301,13 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     double v0 = s.lamx, v1 = s.lamy, v2 = s.lamt;     // value-function gradient
     double l0 = v0, l1 = v1, l2 = v2;                 // true costate
     double dec = 0.0;
+    // the mirror store of stage j+1 is issued one stage late, from registers nothing else wants in between
+    // (issued in place, the next writes to its source registers stalled on the store queue)
+    double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0, p4 = 0.0, p5 = 0.0, p6 = 0.0, p7 = 0.0;
     ring_issue<SS>(m, N - 1, true, 0.0);
     ring_issue<SS>(m, N - 2, N > 1, 0.0);
     for (int j = N - 1; j >= 0; --j) {
+        if (j < N - 1) gg_store(m, j + 1, p0, p1, p2, p3, p4, p5, p6, p7);
         const Stage6 cur = ring_take<SS>(m, j);
         const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1;
         ring_issue<SS>(m, j - 2, j >= 2, ck + cur.pry);      // constants two stages ahead
@@ -338,9 +342,11 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         const double qz0 = gz0 + v0, qz1 = gz1 + v1, qz2 = gz2 + al * v0 + be * v1 + v2;
         double qu0 = gu0 + ck * v0 + sk * v1;
         double qu1 = gu1 + dt * v2;
-        if (c0) { R00 = 1.0; R01 = 0.0; U00 = 0.0; U01 = 0.0; U02 = 0.0; qu0 = 0.0; }
-        if (c1) { R11 = 1.0; R01 = 0.0; U10 = 0.0; U11 = 0.0; U12 = 0.0; qu1 = 0.0; }
-        const double idet = 1.0 / (R00 * R11 - R01 * R01);
+        // frozen inputs: selects, not branches (lanes of a warp freeze different inputs at every stage)
+        R00 = c0 ? 1.0 : R00; U00 = c0 ? 0.0 : U00; U01 = c0 ? 0.0 : U01; U02 = c0 ? 0.0 : U02; qu0 = c0 ? 0.0 : qu0;
+        R11 = c1 ? 1.0 : R11; U10 = c1 ? 0.0 : U10; U11 = c1 ? 0.0 : U11; U12 = c1 ? 0.0 : U12; qu1 = c1 ? 0.0 : qu1;
+        R01 = (c0 || c1) ? 0.0 : R01;
+        const double idet = B2C_RCP(R00 * R11 - R01 * R01);
         const double i00 = R11 * idet, i01 = -R01 * idet, i11 = R00 * idet;
         const double K00 = i00 * U00 + i01 * U10, K01 = i00 * U01 + i01 * U11, K02 = i00 * U02 + i01 * U12;
         const double K10 = i01 * U00 + i11 * U10, K11 = i01 * U01 + i11 * U11, K12 = i01 * U02 + i11 * U12;
@@ -348,7 +354,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         MU(8 * j + 0) = K00; MU(8 * j + 1) = K01; MU(8 * j + 2) = K02;
         MU(8 * j + 3) = K10; MU(8 * j + 4) = K11; MU(8 * j + 5) = K12;
         MU(8 * j + 6) = k0;  MU(8 * j + 7) = k1;
-        gg_store(m, j, K00, K01, K02, K10, K11, K12, k0, k1);
+        p0 = K00; p1 = K01; p2 = K02; p3 = K10; p4 = K11; p5 = K12; p6 = k0; p7 = k1;
         dec += 0.5 * (qu0 * k0 + qu1 * k1);
         s00 = Q00 - (U00 * K00 + U10 * K10);
         s01 = Q01 - (U00 * K01 + U10 * K11);
@@ -360,6 +366,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         v1 = qz1 - (U01 * k0 + U11 * k1);
         v2 = qz2 - (U02 * k0 + U12 * k1);
     }
+    gg_store(m, 0, p0, p1, p2, p3, p4, p5, p6, p7);
     return dec;
 }
 
