@@ -257,6 +257,13 @@ def run_gpu(args):
     except Exception:
         pass
     hbm_peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    traffic = None                  # dram bytes per launch of the dominant kernel, from the committed ncu capture
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_slots_traffic.json")))
+        if args.engine != 1 and tr.get("instances_per_launch") == B:
+            traffic = tr["dram_bytes_per_launch"]
+    except Exception:
+        pass
     avg_launch_s = float(per_launch_ms.mean()) * 1e-3
     achieved_gbs = ALG_BYTES_PER_SOLVE * B / avg_launch_s / 1e9
     fp64_peak = ctx.fma_peak(64)
@@ -292,7 +299,7 @@ def run_gpu(args):
             "solver": {"mean_newton_iters": iters_mean, "optimal_frac": ok_frac, "slack_active_frac": slack_frac,
                        "saturated_u0_frac": sat_frac},
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": which,
+                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": which,
                          "kernel": kernel_name, "avg_launch_ms": avg_launch_s * 1e3,
                          "alg_bytes_per_solve": ALG_BYTES_PER_SOLVE},
             "fp64": {"achieved_tflops": achieved_tf, "peak_tflops_measured": fp64_peak,
