@@ -12,6 +12,8 @@
  *                       (HC/controllers/lqr_controller.py:149-189, :244-257)
  *   b2c_mpc*         <- MPCController.solve_with_ltv (HC/controllers/mpc_controller.py:345-522),
  *                       MPCController.solve (:150-314), _get_fallback_solution (:316-343)
+ *   b2c_rollout_dev  <- the closed-loop loops of run_simulation.py (:58-96, :225-280, :500-570) with
+ *                       RiskMetrics.assess_risk and DifferentialDriveRobot.simulate_step
  *
  * Conventions
  *   - all arithmetic and all real buffers are IEEE fp64 (the reference is numpy fp64);
@@ -140,6 +142,49 @@ int b2c_mpc_host(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
                  int32_t* step_count,
                  double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
                  double* useq, double* xpred);
+
+/* ---- closed-loop rollouts (BASELINE config 5) ------------------------------ */
+/* Replaces the reference's per-robot Python loops (run_simulation.py): run_lqr_simulation :58-96,
+ * run_mpc_simulation :225-280, run_hybrid_simulation :500-570, with RiskMetrics.assess_risk
+ * (HC/controllers/risk_metrics.py:84-222, distance risk; the hybrid loop passes no prediction) and
+ * DifferentialDriveRobot.simulate_step (HC/models/differential_drive.py:138-172) on the device.    */
+enum { B2C_ROLL_LQR = 0, B2C_ROLL_MPC = 1, B2C_ROLL_HYBRID = 2 };
+
+typedef struct {
+    int32_t mode;             /* B2C_ROLL_*                                                        */
+    int32_t ticks;            /* plant steps to simulate                                           */
+    int32_t mpc_rate;         /* MPC mode: solve every mpc_rate ticks and hold (run_simulation.py:243) */
+    int32_t min_dwell;        /* hybrid: ticks a controller is kept after a switch (:520)         */
+    int32_t table_rows;       /* rows of the reference table                                       */
+    int32_t reserved;
+    double  dt;
+    double  plant_v_max, plant_w_max;                 /* DifferentialDriveRobot limits (:52, :160) */
+    double  lqr_Qd[3], lqr_Rd[2], lqr_v_max, lqr_w_max;
+    double  risk_d_safe, risk_d_trigger;
+    double  risk_alpha, risk_beta;                    /* RiskMetrics.alpha / .beta AFTER its constructor normalised
+                                                         them (:76-79); beta multiplies the predictive risk, which the
+                                                         hybrid loop never supplies (always 0)                       */
+    double  risk_threshold_low;
+    b2c_mpc_params mpc;       /* the QP solved on MPC ticks (kind = B2C_MPC_LTV); mpc.M = obstacles per robot */
+} b2c_rollout_params;
+
+/* dev: table (rows,6) row-major [t,px,py,th,v,w] as ReferenceTrajectoryGenerator.generate() returns it;
+ * k0[R] start row per robot (row index is clamped to the last row as get_reference_at_index does);
+ * x[3][R] in: initial states, out: final states; obs[3M][R]; mpc_step_count[R] in/out or NULL (= fresh
+ * controllers).  Outputs: counters[5][R] = lqr_steps, mpc_solves, switches, collision_states,
+ * mpc_fallbacks; stats[3][R] = sum / max / last of the position tracking error norm.  Optional per-tick
+ * logs (NULL to skip): log_x[(ticks+1)][3][R], log_u[ticks][2][R], log_risk[ticks][R],
+ * log_ctrl[ticks][R] (0 = LQR, 1 = MPC).  Synchronous (returns when the rollout has finished).   */
+int b2c_rollout_dev(b2c_ctx*, int64_t R, const b2c_rollout_params* p, const double* table,
+                    const int32_t* k0, double* x, const double* obs, int32_t* mpc_step_count,
+                    int32_t* counters, double* stats,
+                    double* log_x, double* log_u, double* log_risk, int8_t* log_ctrl);
+
+/* host pointers, same [field][robot] layouts */
+int b2c_rollout_host(b2c_ctx*, int64_t R, const b2c_rollout_params* p, const double* table,
+                     const int32_t* k0, double* x, const double* obs, int32_t* mpc_step_count,
+                     int32_t* counters, double* stats,
+                     double* log_x, double* log_u, double* log_risk, int8_t* log_ctrl);
 
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* register-resident FMA microbenchmark: returns achieved TFLOP/s (2 flop per FMA) for fp64

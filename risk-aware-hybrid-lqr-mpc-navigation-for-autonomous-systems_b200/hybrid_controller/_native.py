@@ -36,6 +36,19 @@ class MpcParams(C.Structure):
                 ("w_max", C.c_double), ("dt", C.c_double), ("tol", C.c_double)]
 
 
+class RolloutParams(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("ticks", C.c_int32), ("mpc_rate", C.c_int32), ("min_dwell", C.c_int32),
+                ("table_rows", C.c_int32), ("reserved", C.c_int32), ("dt", C.c_double),
+                ("plant_v_max", C.c_double), ("plant_w_max", C.c_double),
+                ("lqr_Qd", C.c_double * 3), ("lqr_Rd", C.c_double * 2), ("lqr_v_max", C.c_double),
+                ("lqr_w_max", C.c_double),
+                ("risk_d_safe", C.c_double), ("risk_d_trigger", C.c_double), ("risk_alpha", C.c_double),
+                ("risk_beta", C.c_double), ("risk_threshold_low", C.c_double),
+                ("mpc", MpcParams)]
+
+
+ROLL_LQR, ROLL_MPC, ROLL_HYBRID = 0, 1, 2
+
 _P = C.c_void_p
 _D3, _D2 = C.c_double * 3, C.c_double * 2
 # name -> (restype, argtypes); mirrors include/b2c.h one to one
@@ -59,6 +72,8 @@ SIGNATURES = {
     "b2c_mpc_scratch_bytes": (C.c_int64, [C.POINTER(MpcParams), C.c_int64]),
     "b2c_mpc_dev": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
     "b2c_mpc_host": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
+    "b2c_rollout_dev": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
+    "b2c_rollout_host": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
     "b2c_measure_fma_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
 }
 

@@ -15,7 +15,7 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        srcs = [os.path.join(CSRC, f) for f in ("mpc.cu", "mpc_slots.cu", "mpc_args.cuh", "lin_dare.cu", "api.cu", "b2c_common.cuh")]
+        srcs = [os.path.join(CSRC, f) for f in ("mpc.cu", "mpc_slots.cu", "mpc_args.cuh", "lin_dare.cu", "api.cu", "b2c_common.cuh", "rollout.cu")]
         if not os.path.exists(SO) or any(os.path.getmtime(s) > os.path.getmtime(SO) for s in srcs):
             subprocess.check_call(["make", "-C", CSRC, "emul"], stdout=subprocess.DEVNULL)
         _lib = C.CDLL(SO)
@@ -73,3 +73,35 @@ def linearize(v, th, dt, method=1, guard=0):
     p = lambda a: a.ctypes.data_as(C.c_void_p)
     f(B, method, guard, dt, p(v), p(th), p(A), p(Bd))
     return A.T.reshape(B, 3, 3).copy(), Bd.T.reshape(B, 3, 2).copy()
+
+
+def rollout(mode, table, k0, x0, obstacles, ticks, lqr=None, mpc=None, risk=None, mpc_step_count=None, **kw):
+    """Host emulation of b2c_rollout_dev (same per-robot code, emulated K2/K3); same return dict as
+    hybrid_controller.rollout.simulate_batch(log=True)."""
+    from hybrid_controller import _native as nat, rollout as ro
+    table = np.ascontiguousarray(table, np.float64)
+    x0 = np.ascontiguousarray(x0, np.float64).reshape(-1, 3)
+    R = x0.shape[0]
+    k0 = np.ascontiguousarray(np.broadcast_to(np.asarray(k0, np.int32), (R,)))
+    obstacles = np.asarray(obstacles, np.float64)
+    if obstacles.ndim == 2:
+        obstacles = np.broadcast_to(obstacles[None], (R,) + obstacles.shape)
+    M = obstacles.shape[1] if obstacles.size else 0
+    p = ro.rollout_params(mode, ticks, table.shape[0], lqr, mpc, risk, M, **kw)
+    x = np.ascontiguousarray(x0.T)
+    ob = np.ascontiguousarray(obstacles.reshape(R, 3 * M).T) if M else np.zeros((1, R))
+    sc = None if mpc_step_count is None else np.ascontiguousarray(mpc_step_count, np.int32).copy()
+    counters, stats = np.zeros((5, R), np.int32), np.zeros((3, R))
+    lx, lu = np.empty((ticks + 1, 3, R)), np.empty((ticks, 2, R))
+    lr, lc = np.empty((ticks, R)), np.empty((ticks, R), np.int8)
+    f = lib().b2c_emul_rollout
+    f.argtypes = [C.c_int64, C.POINTER(nat.RolloutParams)] + [C.c_void_p] * 11
+    ptr = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    rc = f(R, C.byref(p), ptr(table), ptr(k0), ptr(x), ptr(ob), ptr(sc), ptr(counters), ptr(stats), ptr(lx), ptr(lu),
+           ptr(lr), ptr(lc))
+    assert rc == 0, rc
+    return dict(x=x.T.copy(), lqr_steps=counters[0], mpc_solves=counters[1], switches=counters[2],
+                collision_states=counters[3], mpc_fallbacks=counters[4], mean_error=stats[0] / max(ticks, 1),
+                max_error=stats[1], final_error=stats[2], mpc_step_count=sc,
+                states=lx.transpose(2, 0, 1).copy(), controls=lu.transpose(2, 0, 1).copy(), risk=lr.T.copy(),
+                controller=lc.T.copy())

@@ -116,6 +116,26 @@ def main():
         XN[i] = rob.simulate_step(X[i].copy(), U[i] * 1.7, 0.02)
     res.update(law_x=X, law_xr=XR, law_ur=UR, law_u=U, law_e=E, plant_next=XN)
     np.savez_compressed(os.path.join(OUT, "ref_py.npz"), v=v, th=th, dt=0.02, **res)
+
+    # risk supervisor (HC/controllers/risk_metrics.py) on seeded states, and the one hybrid run log the
+    # reference ships (20260208_003249, run_hybrid_simulation): states / controls / controller tags
+    from hybrid_controller.controllers.risk_metrics import RiskMetrics
+    rm = RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2, threshold_medium=0.5)
+    obs = [dict(x=1.0, y=0.5, radius=0.2), dict(x=-0.5, y=-1.0, radius=0.25), dict(x=1.5, y=-0.3, radius=0.15)]
+    S = rng.uniform(-2.2, 2.2, (200, 3))
+    pred = rng.uniform(-2.2, 2.2, (200, 6, 3)) * 0.5 + S[:, None, :]
+    ra = np.zeros((200, 5)); rp = np.zeros(200)
+    for i in range(200):
+        a_ = rm.assess_risk(S[i], obs)
+        ra[i] = [a_.distance_risk, a_.combined_risk, a_.min_obstacle_distance, a_.nearest_obstacle_id, float(a_.use_mpc)]
+        rp[i] = rm.assess_risk(S[i], obs, pred[i]).combined_risk
+    st, ct, _, _ = read_log("20260208_003249")
+    tags = np.array([1 if r[3] == "MPC" else 0 for r in list(csv.reader(
+        open(f"{REF}/logs/controls_20260208_003249.csv")))[1:]], dtype=np.int8)
+    np.savez_compressed(os.path.join(OUT, "g_hyb.npz"), risk_states=S, risk_pred=pred, risk_out=ra, risk_pred_combined=rp,
+                        risk_alpha=rm.alpha, risk_beta=rm.beta,
+                        states=st[:, 1:4], controls=ct[:, 1:3], controller=tags,
+                        source="logs/{states,controls}_20260208_003249.csv (hybrid_sim) + RiskMetrics on seeded states")
     print("wrote", sorted(os.listdir(OUT)))
 
 
