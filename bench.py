@@ -131,6 +131,91 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
+def secondary_metrics(ctx, dev, stream):
+    """SURVEY 8(d) secondary figures, device-resident, CUDA-event timed on the context's stream (N=1 only):
+    config 3 (2^20 DARE gains, 2^20 linearizations), batch=1 MPC latency at the run_simulation shape (config 2) and a
+    config-5 shard of the hybrid closed loop (65,536 robots x 100 ticks)."""
+    import ctypes as C
+    import torch
+    from hybrid_controller import _native as nat, workloads as wl, rollout as ro
+    from hybrid_controller.controllers import LQRController, MPCController, RiskMetrics
+    out = {}
+
+    def timed(fn, reps):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / reps
+
+    n = 1 << 20
+    v, th = wl.config3_points(n)
+    dv, dth = torch.from_numpy(v).to(dev), torch.from_numpy(th).to(dev)
+    Kd = torch.empty((6, n), dtype=torch.float64, device=dev)
+    Pd = torch.empty((6, n), dtype=torch.float64, device=dev)
+    it = torch.empty(n, dtype=torch.int32, device=dev); st = torch.empty(n, dtype=torch.int32, device=dev)
+    Q, Rr = (C.c_double * 3)(15., 15., 8.), (C.c_double * 2)(.1, .1)
+    t = timed(lambda: ctx.call("b2c_dare_dev", n, nat.LIN_EULER, nat.GUARD_LQR, 0.02, Q, Rr, dv.data_ptr(), dth.data_ptr(),
+                               Kd.data_ptr(), Pd.data_ptr(), it.data_ptr(), st.data_ptr()), 10)
+    flops = 520.0 * float(it.float().mean().item()) + 160.0
+    out["dare_config3"] = {"points": n, "gains_per_s": n / t, "ms": t * 1e3, "mean_doubling_steps": float(it.float().mean().item()),
+                           "ok_frac": float((st == 0).float().mean().item()), "alg_bytes_per_point": 136,
+                           "hbm_gbs": 136 * n / t / 1e9, "fp64_tflops": flops * n / t / 1e12}
+    Ad = torch.empty((9, n), dtype=torch.float64, device=dev); Bd = torch.empty((6, n), dtype=torch.float64, device=dev)
+    t = timed(lambda: ctx.call("b2c_linearize_dev", n, nat.LIN_EULER, nat.GUARD_NONE, 0.02, dv.data_ptr(), dth.data_ptr(),
+                               Ad.data_ptr(), Bd.data_ptr()), 20)
+    out["linearize_config3"] = {"points": n, "points_per_s": n / t, "ms": t * 1e3, "alg_bytes_per_point": 136,
+                                "hbm_gbs": 136 * n / t / 1e9}
+    # batch = 1 latency through the drop-in class (host numpy in/out, wall clock): run_simulation.py --mode mpc shape
+    mpc = MPCController(horizon=6, block_size=2, **wl.SIM_MPC)
+    table = wl.figure8_table()
+    from hybrid_controller.controllers import Obstacle
+    obs = [Obstacle(*o) for o in wl.DEFAULT_OBSTACLES.tolist()]
+    lat = []
+    for k in range(0, 1000, 5):
+        xr, ur = table[k:k + 7, 1:4], table[k:k + 7, 4:6]
+        if len(xr) < 7:
+            break
+        t0 = time.perf_counter()
+        mpc.solve_with_ltv(xr[0] + 0.01, xr, ur, obs)
+        lat.append((time.perf_counter() - t0) * 1e3)
+    lat = np.array(lat[5:])
+    out["mpc_batch1_latency_ms"] = {"mean": float(lat.mean()), "p50": float(np.percentile(lat, 50)),
+                                    "p99": float(np.percentile(lat, 99)), "solves": int(lat.size),
+                                    "reference_shipped_log_mean_ms": 82.6}
+    # config-5 shard
+    R, T = 65536, 100
+    rng = np.random.default_rng(0)
+    k0 = rng.integers(0, 500, R).astype(np.int32)
+    x0 = table[k0, 1:4] + rng.uniform(-1, 1, (R, 3)) * np.array([.1, .1, .2])
+    ob = np.broadcast_to(wl.DEFAULT_OBSTACLES[None], (R, 3, 3)).copy()
+    ob[:, :, :2] += rng.uniform(-.2, .2, (R, 3, 2))
+    p = ro.rollout_params("hybrid", T, table.shape[0], LQRController(**wl.SIM_LQR),
+                          MPCController(horizon=6, block_size=1, **wl.SIM_MPC),
+                          RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2, threshold_medium=0.5), 3)
+    d_tab = torch.from_numpy(table).to(dev); d_k0 = torch.from_numpy(k0).to(dev)
+    d_ob = torch.from_numpy(np.ascontiguousarray(ob.reshape(R, 9).T)).to(dev)
+    x_init = torch.from_numpy(np.ascontiguousarray(x0.T)).to(dev)
+    cnt = torch.zeros((5, R), dtype=torch.int32, device=dev); sts = torch.zeros((3, R), dtype=torch.float64, device=dev)
+    best = 1e9
+    for _ in range(3):
+        d_x = x_init.clone(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ctx.call("b2c_rollout_dev", R, C.byref(p), d_tab.data_ptr(), d_k0.data_ptr(), d_x.data_ptr(), d_ob.data_ptr(), None,
+                 cnt.data_ptr(), sts.data_ptr(), None, None, None, None)
+        torch.cuda.synchronize()
+        best = min(best, time.perf_counter() - t0)
+    c = cnt.sum(dim=1).cpu().numpy().astype(float)
+    out["hybrid_rollout_config5_shard"] = {"robots": R, "ticks": T, "robot_steps_per_s": R * T / best,
+                                           "mpc_solve_fraction": c[1] / (R * T), "switches_per_robot": c[2] / R,
+                                           "collision_state_fraction": c[3] / (R * (T + 1)),
+                                           "mean_tracking_error_m": float((sts[0] / T).mean().item()),
+                                           "note": "tools/bench_rollout.py runs the full 1,048,576 x 500 shard"}
+    return out
+
+
 def run_gpu(args):
     import ctypes as C
     import torch
@@ -287,6 +372,10 @@ def run_gpu(args):
                          "(HiGHS + KKT polish); cvxpy/OSQP absent from the image",
                "max_abs_u0_diff_vs_gpu": parity}
 
+    secondary = None
+    if world == 1 and not args.no_secondary:
+        secondary = secondary_metrics(ctx, dev, stream)
+
     line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
@@ -312,6 +401,8 @@ def run_gpu(args):
             "wall_s_timed_region": t_wall}
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if secondary is not None:
+        line["secondary"] = secondary
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -324,6 +415,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary (DARE / linearize / rollout) figures")
     ap.add_argument("--engine", type=int, default=0, choices=[0, 1, 2],
                     help="K3 kernel: 0 auto (slot kernel for this shape), 1 general kernel, 2 slot kernel")
     args = ap.parse_args()

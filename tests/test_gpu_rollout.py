@@ -38,7 +38,12 @@ def test_rollout_mpc_mode_vs_g_mpc(golden):
     out = simulate_batch("mpc", table, [0], table[0:1, 1:4], np.array(DEFAULT_OBS), 998, mpc=mpc, mpc_rate=5, log=True)
     assert np.abs(out["states"][0] - g["states"][:999]).max() < 5e-4           # the log's own OSQP eps re-enters the loop
     assert np.abs(out["controls"][0] - g["controls"][:998]).max() < 5e-3
-    assert out["mpc_solves"][0] == 200 and out["mpc_fallbacks"][0] == 0 and out["collision_states"][0] == 0
+    assert out["mpc_solves"][0] == 200 and out["mpc_fallbacks"][0] == 0
+    # collision census of run_mpc_simulation (:288-293): states inside radius + d_safe of any obstacle
+    ob = np.array(DEFAULT_OBS)
+    inside = (np.linalg.norm(out["states"][0][:, None, :2] - ob[None, :, :2], axis=2) < ob[:, 2] + 0.3).any(axis=1)
+    assert out["collision_states"][0] == inside.sum() == (np.linalg.norm(
+        g["states"][:999, None, :2] - ob[None, :, :2], axis=2) < ob[:, 2] + 0.3).any(axis=1).sum()
 
 
 def test_rollout_hybrid_vs_emulation_and_oracle():
