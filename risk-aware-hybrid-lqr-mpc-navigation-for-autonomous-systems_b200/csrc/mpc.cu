@@ -500,7 +500,7 @@ int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B) {
     int tpb = 0;
     if (p->engine != B2C_MPC_ENGINE_GENERAL && mpc_slots_eligible(a, &tpb)) {
         // slot kernel: G[6N] + GG[8N] doubles per RESIDENT slot (one CTA per SM, 148 SMs assumed here)
-        int64_t slots = (B + tpb - 1) / tpb; if (slots > 148) slots = 148;
+        int64_t slots = (B + tpb - 1) / tpb; if (slots > 2 * 148) slots = 2 * 148;   // upper bound
         return (int64_t)14 * p->N * slots * tpb * (int64_t)sizeof(double) + 256;
     }
     return (int64_t)mpc_fields(p) * B * (int64_t)sizeof(double);

@@ -722,7 +722,10 @@ static int slots_launch_t(b2c_ctx* ctx, const MpcArgs& a, int grid, size_t smem)
 int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     const size_t smem = (size_t)(slot_fields(a) + 12) * tpb * sizeof(double);
     int grid = (int)((a.B + tpb - 1) / tpb);
-    if (grid > ctx->sm_count) grid = ctx->sm_count;
+    // short horizons leave room for a second resident CTA per SM (two warps per scheduler hide the dependent-issue
+    // latency of the sweeps); registers allow two CTAs of 128 threads, shared memory decides
+    const int per_sm = (tpb == 128 && 2 * (smem + 1024) <= (size_t)227 * 1024) ? 2 : 1;
+    if (grid > per_sm * ctx->sm_count) grid = per_sm * ctx->sm_count;
     a.nslots = (int64_t)grid * tpb;
     // global strips: G[6N] + GG[8N] doubles per slot, then the queue counter
     const size_t strip = (size_t)(14 * a.N) * (size_t)a.nslots * sizeof(double);

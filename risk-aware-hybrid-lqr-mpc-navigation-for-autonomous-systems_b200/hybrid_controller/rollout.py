@@ -78,3 +78,41 @@ def simulate_batch(mode: str, table, k0, x0, obstacles, ticks: int, lqr=None, mp
         out.update(states=lx.transpose(2, 0, 1).copy(), controls=lu.transpose(2, 0, 1).copy(), risk=lr.T.copy(),
                    controller=lc.T.copy())
     return out
+
+
+def export_robot_csv(out: Dict[str, Any], r: int, table, k0: int, log_dir: str, stamp: str, mode: str = "hybrid",
+                     wrap_error: Optional[bool] = None):
+    """Write robot r of a simulate_batch(log=True) result in the reference's run-log schema
+    (HC/logging/simulation_logger.py:174-186 states, :221-227 controls, csv.DictWriter as :402-452), so that one robot
+    of a batch can be diffed against a reference run with the tooling used on its shipped logs.
+
+    states_<stamp>.csv  : timestep,px,py,theta,px_ref,py_ref,theta_ref,error_px,error_py,error_theta,error_norm
+    controls_<stamp>.csv: timestep,v,omega,controller,solve_time_ms
+    The heading error is wrapped in the lqr / mpc loops and left raw in the hybrid loop (run_simulation.py:562, Q12)."""
+    import csv
+    import os
+    table = np.asarray(table, float)
+    states, controls, which = out["states"][r], out["controls"][r], out["controller"][r]
+    wrap = (mode != "hybrid") if wrap_error is None else wrap_error
+    os.makedirs(log_dir, exist_ok=True)
+    ps, pc = os.path.join(log_dir, f"states_{stamp}.csv"), os.path.join(log_dir, f"controls_{stamp}.csv")
+    with open(ps, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["timestep", "px", "py", "theta", "px_ref", "py_ref", "theta_ref", "error_px", "error_py",
+                    "error_theta", "error_norm"])
+        for t in range(len(controls)):
+            ref = table[min(k0 + t, len(table) - 1), 1:4]
+            e = states[t] - ref
+            if wrap:
+                while e[2] > np.pi:
+                    e[2] -= 2 * np.pi
+                while e[2] < -np.pi:
+                    e[2] += 2 * np.pi
+            w.writerow([t] + [float(v) for v in states[t]] + [float(v) for v in ref] + [float(v) for v in e]
+                       + [float(np.linalg.norm(e))])
+    with open(pc, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["timestep", "v", "omega", "controller", "solve_time_ms"])
+        for t in range(len(controls)):
+            w.writerow([t, float(controls[t, 0]), float(controls[t, 1]), "MPC" if which[t] else "LQR", ""])
+    return ps, pc

@@ -116,3 +116,26 @@ def test_emul_rollout_end_of_table_and_counters():
     o = oro.simulate("hybrid", table, 90, table[90, 1:4], obs, 20, mpc_prm=dict(MPC_PRM6, block_size=1), step_count=3)
     assert np.abs(out["states"][0] - o["states"]).max() < 1e-7 and np.array_equal(out["controller"][0], o["controller"])
     assert out["mpc_step_count"][0] == o["step_count"] and out["mpc_step_count"][1] == out["mpc_solves"][1]
+
+
+def test_export_robot_csv_matches_reference_log_schema(golden, tmp_path):
+    """One robot of a batch written in the SimulationLogger CSV schema: header identical to the shipped logs, rows
+    equal to G-LQR's (reference columns exactly, states / errors to the closed-loop tolerance)."""
+    import csv
+    from hybrid_controller.rollout import export_robot_csv
+    g = golden["g_lqr"]
+    lqr, _, _ = _controllers()
+    table = lin_dare.figure8(20.0)
+    out = emul.rollout("lqr", table, [0, 3], table[[0, 3], 1:4], np.zeros((0, 3)), 998, lqr=lqr)
+    ps, pc = export_robot_csv(out, 0, table, 0, str(tmp_path), "test", mode="lqr")
+    rows = list(csv.reader(open(ps)))
+    assert rows[0] == ["timestep", "px", "py", "theta", "px_ref", "py_ref", "theta_ref", "error_px", "error_py",
+                       "error_theta", "error_norm"]
+    a = np.array([[float(v) for v in r] for r in rows[1:]])
+    assert len(a) == 998 and np.array_equal(a[:, 0], np.arange(998))
+    assert np.abs(a[:, 1:4] - g["states"][:998]).max() < 1e-9 and np.abs(a[:, 4:7] - g["refs"][:998]).max() < 1e-12
+    assert np.abs(a[:, 7:10] - g["errors"][:998]).max() < 1e-9
+    assert np.abs(a[:, 10] - np.linalg.norm(g["errors"][:998], axis=1)).max() < 1e-9
+    crow = list(csv.reader(open(pc)))
+    assert crow[0] == ["timestep", "v", "omega", "controller", "solve_time_ms"] and crow[1][3] == "LQR" and crow[1][4] == ""
+    assert np.abs(np.array([[float(r[1]), float(r[2])] for r in crow[1:]]) - g["controls"][:998]).max() < 1e-9
