@@ -1,5 +1,6 @@
 // Context lifecycle, host-buffer entry points (pinned staging + on-device re-layout) and the
 // FMA-peak microbenchmark of libb2c.so.
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include "b2c_common.cuh"
@@ -69,6 +70,12 @@ void b2c_destroy(b2c_ctx* c) {
     if (c->scratch) cudaFree(c->scratch);
     if (c->dstage) cudaFree(c->dstage);
     if (c->hstage) cudaFreeHost(c->hstage);
+    for (int k = 0; k < 2; ++k) {
+        if (c->lane_scratch[k]) cudaFree(c->lane_scratch[k]);
+        if (c->lane_stream[k]) cudaStreamDestroy(c->lane_stream[k]);
+    }
+    if (c->out_stream) cudaStreamDestroy(c->out_stream);
+    for (int k = 0; k < 16; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -218,6 +225,31 @@ int b2c_dare_host(b2c_ctx* c, int64_t B, int method, int guard, double dt,
     return 0;
 }
 
+// While alive, the context launches on compute lane k: its stream and its private K3 scratch.
+struct LaneScope {
+    b2c_ctx* c; int k; cudaStream_t s0; void* sc0; size_t sb0;
+    LaneScope(b2c_ctx* c_, int k_) : c(c_), k(k_), s0(c_->stream), sc0(c_->scratch), sb0(c_->scratch_bytes) {
+        c->stream = c->lane_stream[k]; c->scratch = c->lane_scratch[k]; c->scratch_bytes = c->lane_scratch_bytes[k];
+    }
+    ~LaneScope() {
+        c->lane_scratch[k] = c->scratch; c->lane_scratch_bytes[k] = c->scratch_bytes;
+        c->stream = s0; c->scratch = sc0; c->scratch_bytes = sb0;
+    }
+};
+
+static int pipeline_init(b2c_ctx* c) {
+    for (int k = 0; k < 2; ++k)
+        if (!c->lane_stream[k]) B2C_CUDA(cudaStreamCreateWithFlags(&c->lane_stream[k], cudaStreamNonBlocking));
+    if (!c->out_stream) B2C_CUDA(cudaStreamCreateWithFlags(&c->out_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 16; ++k)
+        if (!c->ev[k]) B2C_CUDA(cudaEventCreateWithFlags(&c->ev[k], cudaEventDisableTiming));
+    return 0;
+}
+
+// Host entry point of K3.  Large batches are cut into chunks of consecutive instances that flow through a
+// three-stage pipeline -- H2D copies on the context's stream, re-layout + solve on two alternating compute lanes
+// (so the tail of one chunk's persistent kernel overlaps the next chunk), D2H on an output stream -- which hides
+// most of the solve behind the PCIe transfer of the inputs (63 MB per 65,536 config-4 instances).
 int b2c_mpc_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
                  const double* x0, const double* xref, const double* uref, const double* obs,
                  int32_t* step_count,
@@ -245,35 +277,65 @@ int b2c_mpc_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
     double* s_xp = xpred ? bp.take<double>(FX * B) : nullptr; double* a_xp = xpred ? bp.take<double>(FX * B) : nullptr;
     int32_t* d_sc = bp.take<int32_t>(B); int32_t* d_st = bp.take<int32_t>(B);
     int32_t* d_it = bp.take<int32_t>(B); int32_t* d_sl = bp.take<int32_t>(B);
-    cudaStream_t s = c->stream;
-    B2C_CUDA(cudaMemcpyAsync(a_x0, x0, (size_t)B * 3 * 8, cudaMemcpyHostToDevice, s));
-    B2C_CUDA(cudaMemcpyAsync(a_xr, xref, (size_t)B * FX * 8, cudaMemcpyHostToDevice, s));
-    B2C_CUDA(cudaMemcpyAsync(a_ur, uref, (size_t)B * FU * 8, cudaMemcpyHostToDevice, s));
-    if (FO) B2C_CUDA(cudaMemcpyAsync(a_ob, obs, (size_t)B * FO * 8, cudaMemcpyHostToDevice, s));
-    if (step_count) B2C_CUDA(cudaMemcpyAsync(d_sc, step_count, (size_t)B * 4, cudaMemcpyHostToDevice, s));
-    if ((rc = to_soa(c, B, 3, a_x0, s_x0))) return rc;
-    if ((rc = to_soa(c, B, FX, a_xr, s_xr))) return rc;
-    if ((rc = to_soa(c, B, FU, a_ur, s_ur))) return rc;
-    if ((rc = to_soa(c, B, FO, a_ob, s_ob))) return rc;
-    rc = b2c_mpc_dev(c, B, p, s_x0, s_xr, s_ur, s_ob, step_count ? d_sc : nullptr,
-                     s_u0, d_cost, d_st, d_it, d_sl, s_us, s_xp);
-    if (rc) return rc;
-    if ((rc = to_aos(c, B, 2, s_u0, a_u0))) return rc;
-    B2C_CUDA(cudaMemcpyAsync(u0, a_u0, (size_t)B * 2 * 8, cudaMemcpyDeviceToHost, s));
-    B2C_CUDA(cudaMemcpyAsync(cost, d_cost, (size_t)B * 8, cudaMemcpyDeviceToHost, s));
-    if (useq) {
-        if ((rc = to_aos(c, B, FU, s_us, a_us))) return rc;
-        B2C_CUDA(cudaMemcpyAsync(useq, a_us, (size_t)B * FU * 8, cudaMemcpyDeviceToHost, s));
+    // chunks: a multiple of 32 instances each, at most 8, none smaller than 8,192 instances
+    int C = (int)(B / 16384);
+    if (C > 8) C = 8;
+    if (C < 2) C = 1;
+    if (const char* e = getenv("B2C_HOST_CHUNKS")) { int v = atoi(e); if (v >= 1 && v <= 8 && B >= 64 * v) C = v; }
+    if (C > 1 && (rc = pipeline_init(c))) return rc;
+    const int64_t per = C > 1 ? ((B / C + 31) / 32) * 32 : B;
+    cudaStream_t s_in = c->stream;
+    for (int ch = 0; ch < C; ++ch) {
+        const int64_t i0 = (int64_t)ch * per, Bc = (ch == C - 1) ? B - i0 : per;
+        if (Bc <= 0) break;
+        // chunk-local SoA blocks sit at offset F*i0 of the full-size buffers (sum of F*Bc over chunks = F*B)
+        double* cx0 = s_x0 + 3 * i0; double* cxr = s_xr + (int64_t)FX * i0; double* cur = s_ur + (int64_t)FU * i0;
+        double* cob = s_ob + (int64_t)FO * i0; double* cu0 = s_u0 + 2 * i0;
+        double* cus = useq ? s_us + (int64_t)FU * i0 : nullptr; double* cxp = xpred ? s_xp + (int64_t)FX * i0 : nullptr;
+        B2C_CUDA(cudaMemcpyAsync(a_x0 + 3 * i0, x0 + 3 * i0, (size_t)Bc * 3 * 8, cudaMemcpyHostToDevice, s_in));
+        B2C_CUDA(cudaMemcpyAsync(a_xr + FX * i0, xref + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyHostToDevice, s_in));
+        B2C_CUDA(cudaMemcpyAsync(a_ur + FU * i0, uref + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyHostToDevice, s_in));
+        if (FO) B2C_CUDA(cudaMemcpyAsync(a_ob + FO * i0, obs + FO * i0, (size_t)Bc * FO * 8, cudaMemcpyHostToDevice, s_in));
+        if (step_count) B2C_CUDA(cudaMemcpyAsync(d_sc + i0, step_count + i0, (size_t)Bc * 4, cudaMemcpyHostToDevice, s_in));
+        cudaStream_t s_out = s_in;
+        {
+            const int lane = ch & 1;
+            if (C > 1) {
+                B2C_CUDA(cudaEventRecord(c->ev[ch], s_in));
+                B2C_CUDA(cudaStreamWaitEvent(c->lane_stream[lane], c->ev[ch], 0));
+            }
+            struct Maybe { LaneScope* l; ~Maybe() { delete l; } } scope{C > 1 ? new LaneScope(c, lane) : nullptr};
+            if ((rc = to_soa(c, Bc, 3, a_x0 + 3 * i0, cx0))) return rc;
+            if ((rc = to_soa(c, Bc, FX, a_xr + FX * i0, cxr))) return rc;
+            if ((rc = to_soa(c, Bc, FU, a_ur + FU * i0, cur))) return rc;
+            if ((rc = to_soa(c, Bc, FO, a_ob + FO * i0, cob))) return rc;
+            rc = b2c_mpc_dev(c, Bc, p, cx0, cxr, cur, cob, step_count ? d_sc + i0 : nullptr,
+                             cu0, d_cost + i0, d_st + i0, d_it + i0, d_sl + i0, cus, cxp);
+            if (rc) return rc;
+            if ((rc = to_aos(c, Bc, 2, cu0, a_u0 + 2 * i0))) return rc;
+            if (useq && (rc = to_aos(c, Bc, FU, cus, a_us + FU * i0))) return rc;
+            if (xpred && (rc = to_aos(c, Bc, FX, cxp, a_xp + FX * i0))) return rc;
+            if (C > 1) {
+                B2C_CUDA(cudaEventRecord(c->ev[8 + ch], c->stream));
+                B2C_CUDA(cudaStreamWaitEvent(c->out_stream, c->ev[8 + ch], 0));
+                s_out = c->out_stream;
+            }
+        }
+        B2C_CUDA(cudaMemcpyAsync(u0 + 2 * i0, a_u0 + 2 * i0, (size_t)Bc * 2 * 8, cudaMemcpyDeviceToHost, s_out));
+        B2C_CUDA(cudaMemcpyAsync(cost + i0, d_cost + i0, (size_t)Bc * 8, cudaMemcpyDeviceToHost, s_out));
+        if (useq) B2C_CUDA(cudaMemcpyAsync(useq + FU * i0, a_us + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyDeviceToHost, s_out));
+        if (xpred) B2C_CUDA(cudaMemcpyAsync(xpred + FX * i0, a_xp + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyDeviceToHost, s_out));
+        if (status) B2C_CUDA(cudaMemcpyAsync(status + i0, d_st + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
+        if (iters) B2C_CUDA(cudaMemcpyAsync(iters + i0, d_it + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
+        if (slack_used) B2C_CUDA(cudaMemcpyAsync(slack_used + i0, d_sl + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
+        if (step_count) B2C_CUDA(cudaMemcpyAsync(step_count + i0, d_sc + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
     }
-    if (xpred) {
-        if ((rc = to_aos(c, B, FX, s_xp, a_xp))) return rc;
-        B2C_CUDA(cudaMemcpyAsync(xpred, a_xp, (size_t)B * FX * 8, cudaMemcpyDeviceToHost, s));
+    if (C > 1) {
+        B2C_CUDA(cudaStreamSynchronize(c->out_stream));
+        B2C_CUDA(cudaStreamSynchronize(c->lane_stream[0]));
+        B2C_CUDA(cudaStreamSynchronize(c->lane_stream[1]));
     }
-    if (status) B2C_CUDA(cudaMemcpyAsync(status, d_st, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
-    if (iters) B2C_CUDA(cudaMemcpyAsync(iters, d_it, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
-    if (slack_used) B2C_CUDA(cudaMemcpyAsync(slack_used, d_sl, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
-    if (step_count) B2C_CUDA(cudaMemcpyAsync(step_count, d_sc, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
-    B2C_CUDA(cudaStreamSynchronize(s));
+    B2C_CUDA(cudaStreamSynchronize(s_in));
     return 0;
 }
 

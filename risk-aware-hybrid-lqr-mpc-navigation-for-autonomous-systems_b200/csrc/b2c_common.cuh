@@ -21,6 +21,13 @@ struct b2c_ctx {
     void* hstage = nullptr;
     size_t hstage_bytes = 0;
     int64_t launches = 0;
+    // chunk pipeline of the *_host entry points: two compute lanes (stream + private K3 scratch) and an output
+    // stream, created on first use; events are reused
+    cudaStream_t lane_stream[2] = {nullptr, nullptr};
+    cudaStream_t out_stream = nullptr;
+    void* lane_scratch[2] = {nullptr, nullptr};
+    size_t lane_scratch_bytes[2] = {0, 0};
+    cudaEvent_t ev[16] = {};
 };
 
 void b2c_set_error(const std::string& s);
