@@ -64,7 +64,9 @@ typedef struct {
     int32_t N;                /* horizon                      (mpc_controller.py:111)           */
     int32_t M;                /* obstacles per instance (0 allowed)                             */
     int32_t block_size;       /* move blocking, LTV only      (:118-121)                        */
-    int32_t soft;             /* use_soft_constraints         (:152, :347)                      */
+    int32_t soft;             /* use_soft_constraints (:152, :347).  0 = hard obstacle rows (:197-200, :260-270,
+                                 :383-386, :464-468): solved by the method of multipliers in the general kernel;
+                                 rows that cannot be met give status B2C_INFEASIBLE and the fallback outputs   */
     int32_t max_iter;         /* Newton iteration cap (<=0: default 60)                         */
     int32_t ramp_up_steps;    /* cold-start ramp length       (:144), LTV only                  */
     int32_t engine;           /* kernel choice: 0 = automatic, 1 = general kernel (HBM scratch), 2 = persistent

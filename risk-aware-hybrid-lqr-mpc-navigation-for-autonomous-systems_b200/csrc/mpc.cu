@@ -34,16 +34,26 @@ template <bool BS1> struct Lay {
 // Rolls the plant out from z0 under either the current inputs (USE_GAIN=false) or the Newton
 // update  w+ = clip(w - alpha*kf - K (z+ - z))  (USE_GAIN=true, written to buffer `dst`), and
 // accumulates cost + the per-super-stage quadratic model at the NEW trajectory.
+//
+// Hard rows (use_soft_constraints=False, :197-200 / :260-270 / :383-386 / :464-468) are handled by the method of
+// multipliers on the same machinery: with multiplier lm >= 0 and penalty mu a row contributes
+//   (mu/2) * max(0, g + lm/mu)^2      (g = d_safe + r - n.(p - o), the row's violation),
+// i.e. exactly the soft row with rho -> mu/2 and a shifted threshold.  `mu` = 0 selects the soft formula;
+// `update` applies lm <- max(0, lm + mu*g) in place before evaluating.  In hard mode `max_viol` returns the KKT
+// residual max |max(g, -lm/mu)| (primal violation and complementarity) and `J0` the objective without row terms.
 template <bool BS1, bool USE_GAIN>
 B2C_HD double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, double z0t,
                                               int src, int dst, double alpha, double& max_viol,
-                                              bool& infeasible, double& lamx, double& lamy, double& lamt) {
+                                              bool& infeasible, double& lamx, double& lamy, double& lamt,
+                                              const double mu = 0.0, const bool update = false, double* J0out = nullptr) {
     using L = Lay<BS1>;
     const int N = a.N, Nb = a.Nb, M = a.M;
     const bool ltv = (a.kind == B2C_MPC_LTV);
     double zx = z0x, zy = z0y, zt = z0t;          // new trajectory
     double ox_ = z0x, oy_ = z0y, ot_ = z0t;       // old trajectory (only with gains)
-    double J = 0.0;
+    double J = 0.0, Jrows = 0.0;
+    const bool hard = mu > 0.0;
+    const double rho = hard ? 0.5 * mu : a.rho;
     max_viol = 0.0;
     for (int j = 0; j < Nb; ++j) {
         const int k_begin = j * a.bs;
@@ -104,10 +114,19 @@ B2C_HD double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, d
                     // LTV: p = p_ref + dz  => n.(p - o) = dist + n.dz ;  LTI: p = z
                     double lhs = ltv ? (d2 * inv + nx * zx + ny * zy) : (nx * (zx - obx) + ny * (zy - oby));
                     double viol = (a.d_safe + obr) - lhs;
-                    if (viol > 0.0) {
+                    if (hard) {
+                        if (k == 0 && viol > 1e-6) infeasible = true;      // a row on the fixed initial state
+                        const int lf = a.lam_off + k * M + m;
+                        double lm = SC(lf);
+                        max_viol = fmax(max_viol, fabs(fmax(viol, -lm / mu)));
+                        if (update) { lm = fmax(0.0, lm + mu * viol); SC(lf) = lm; }
+                        viol += lm / mu;
+                    } else if (viol > 0.0) {
                         max_viol = fmax(max_viol, viol);
-                        J += a.rho * viol * viol;
-                        const double rn0 = a.rho * nx, rn1 = a.rho * ny;
+                    }
+                    if (viol > 0.0) {
+                        Jrows += rho * viol * viol;
+                        const double rn0 = rho * nx, rn1 = rho * ny;
                         wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
                         gx -= rn0 * viol; gy -= rn1 * viol;
                     }
@@ -171,7 +190,8 @@ B2C_HD double mpc_forward(const MpcArgs& a, int64_t i, double z0x, double z0y, d
     }
     J += a.p0 * ex * ex + a.p1 * ey * ey + a.p2 * et * et;
     lamx = a.p0 * ex; lamy = a.p1 * ey; lamt = a.p2 * et;
-    return J;
+    if (J0out) *J0out = J;
+    return J + Jrows;
 }
 
 // ----- backward pass --------------------------------------------------------------------------
@@ -375,9 +395,15 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
     }
 
     // ---- Newton loop (state machine so that a warp's lanes share each pass) --------------------
+    // hard rows: method of multipliers around it -- lm = 0, mu = 2 rho (the soft problem) to start with
+    const bool hard = !a.soft && a.M > 0;
+    double mu = hard ? 2.0 * a.rho : 0.0, J0 = 0.0, res_prev = 1e300;
+    int outer = 0;
+    if (hard) for (int e = 0; e < N * a.M; ++e) SC(a.lam_off + e) = 0.0;
     int cur = 0, it = 0, st = B2C_MAXITER;
     double lamx, lamy, lamt, max_viol = 0.0;
-    double J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, infeasible, lamx, lamy, lamt);
+    double J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, infeasible, lamx, lamy, lamt,
+                                       mu, false, &J0);
     bool active = true;
     if (infeasible) { st = B2C_INFEASIBLE; active = false; }
     if (!(fabs(J) < 1e300)) { st = B2C_NONFINITE; active = false; }
@@ -388,16 +414,36 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
         if (need_backward) {
             dec = mpc_backward<BS1>(a, i, cur, lamx, lamy, lamt);
             if (!(dec < 1e300)) { st = B2C_NONFINITE; break; }
-            if (dec <= a.tol * fmax(1.0, fabs(J))) { st = B2C_OK; break; }
+            if (dec <= a.tol * fmax(1.0, fabs(J))) {
+                if (!hard || max_viol <= MPC_HARD_TOL) { st = B2C_OK; break; }
+                // inner problem solved, rows not yet feasible / complementary: multiplier step.  A residual
+                // that does not drop fourfold asks for a stiffer penalty; no progress at the stiffest means the
+                // rows cannot be met (the reference's solver reports infeasible -> fallback)
+                if (++outer > MPC_HARD_OUTER || (mu >= 1e11 && max_viol > 0.5 * res_prev)) { st = B2C_INFEASIBLE; break; }
+                const bool stiffer = max_viol > 0.25 * res_prev && mu < 1e11;
+                res_prev = max_viol;
+                bool dummy = false;
+                J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, dummy, lamx, lamy, lamt,
+                                            mu, true, &J0);
+                if (stiffer) {
+                    mu *= 10.0;
+                    J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, dummy, lamx, lamy, lamt,
+                                                mu, false, &J0);
+                }
+                if (!(fabs(J) < 1e300)) { st = B2C_NONFINITE; break; }
+                continue;
+            }
             if (it >= a.max_iter) { st = B2C_MAXITER; break; }
             alpha = (it == 0) ? 1.0 : fmin(1.0, MPC_LS_GROW * alpha);
             ++it; ls = 0; need_backward = false;
         }
         double tlx, tly, tlt, tviol;
         bool dummy = false;
-        const double Jn = mpc_forward<BS1, true>(a, i, z0x, z0y, z0t, cur, cur ^ 1, alpha, tviol, dummy, tlx, tly, tlt);
+        double tJ0 = 0.0;
+        const double Jn = mpc_forward<BS1, true>(a, i, z0x, z0y, z0t, cur, cur ^ 1, alpha, tviol, dummy, tlx, tly, tlt,
+                                                 mu, false, &tJ0);
         if (Jn < J) {
-            J = Jn; cur ^= 1; lamx = tlx; lamy = tly; lamt = tlt; max_viol = tviol; need_backward = true;
+            J = Jn; J0 = tJ0; cur ^= 1; lamx = tlx; lamy = tly; lamt = tlt; max_viol = tviol; need_backward = true;
         } else {
             alpha *= 0.5;
             ++ls;
@@ -417,7 +463,8 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
         const double w0 = SC(L::w(N, Nb, cur, 0)), w1 = SC(L::w(N, Nb, cur, 0) + 1);
         u00 = ltv ? (ur00 + w0) : w0;
         u01 = ltv ? (ur01 + w1) : w1;
-        Jout = J;
+        Jout = hard ? J0 : J;                    // problem.value: no slack term in the hard problem
+        if (hard) max_viol = 0.0;                // slack_used is False without slack variables, :294-296
         if (a.useq || a.xpred) {                 // :484-498: un-block, add the (wrapped) references
             double zx = z0x, zy = z0y, zt = z0t;
             for (int k = 0; k <= N; ++k) {
@@ -489,7 +536,8 @@ k_mpc(const MpcArgs a) {
 static int mpc_fields(const b2c_mpc_params* p) {
     const int bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
     const int Nb = (p->N + bs - 1) / bs;
-    return bs == 1 ? Lay<true>::total(p->N, Nb) : Lay<false>::total(p->N, Nb);
+    const int lam = (!p->soft && p->M > 0) ? p->N * p->M : 0;      // one multiplier per hard row
+    return (bs == 1 ? Lay<true>::total(p->N, Nb) : Lay<false>::total(p->N, Nb)) + lam;
 }
 
 int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B) {
@@ -514,10 +562,6 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     if (!ctx || !p) { b2c_set_error("null context/params"); return -1; }
     if (p->N < 1 || p->N > 4096 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
     if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
-    if (!p->soft && p->M > 0) {
-        b2c_set_error("hard obstacle constraints (use_soft_constraints=False) are not implemented yet");
-        return -4;
-    }
     if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
     if (B <= 0) return 0;
     MpcArgs a;
@@ -533,6 +577,7 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, need, false);
     if (rc) return rc;
     a.scratch = (double*)ctx->scratch;
+    a.lam_off = mpc_fields(p) - ((!p->soft && p->M > 0) ? p->N * p->M : 0);
     if (a.bs == 1) k_mpc<true><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
     else           k_mpc<false><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
     B2C_CHECK_LAUNCH(ctx);
@@ -550,6 +595,7 @@ extern "C" int b2c_emul_mpc(int64_t B, const b2c_mpc_params* p,
     mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
     std::vector<double> scratch((size_t)mpc_fields(p) * (size_t)B);
     a.scratch = scratch.data();
+    a.lam_off = mpc_fields(p) - ((!p->soft && p->M > 0) ? p->N * p->M : 0);
     for (int64_t i = 0; i < B; ++i) {
         if (a.bs == 1) mpc_solve_one<true>(a, i); else mpc_solve_one<false>(a, i);
     }

@@ -422,3 +422,39 @@ def test_mpc_config2_closed_loop_vs_g_mpc(hc, golden):
     print(f"\nbatch=1 solve_with_ltv latency: mean {lat.mean():.3f} ms  p50 {np.median(lat):.3f}  p99 "
           f"{np.percentile(lat, 99):.3f} ms   (reference log: mean 82.6 ms, p99 154.5 ms)")
     assert np.median(lat) < 5.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,bs,M", [(20, 1, 5), (6, 2, 3)])
+def test_mpc_hard_rows_vs_oracle_and_emulation(hc, N, bs, M):
+    """use_soft_constraints=False on the device (method of multipliers in k_mpc): batch against the host emulation of
+    the same code, a subset against the oracle's exact QP, and the scalar drop-in call incl. an infeasible instance
+    (status "fallback", cost inf, as the reference returns when its solver reports infeasible)."""
+    import emul
+    from hybrid_controller.controllers.mpc_controller import MPCController, Obstacle
+    from hybrid_controller import workloads as wl, _native as nat
+    B = 2048
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=77, obstacles=wl.DENSE_OBSTACLES[:M])
+    mpc = MPCController(horizon=N, block_size=bs, **wl.SIM_MPC)
+    out = mpc.solve_with_ltv_batch(x0, xr, ur, ob, use_soft_constraints=False)
+    p = nat.mpc_params(nat.MPC_LTV, N, M, bs, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02, soft=False)
+    ref = emul.mpc(p, x0, xr, ur, ob)
+    assert np.array_equal(out["status"], ref["status"]) and set(np.unique(out["status"])) == {0, 3}
+    ok = out["status"] == 0
+    assert np.abs(out["u0"] - ref["u0"]).max() <= 1e-7 and np.abs(out["xpred"][ok] - ref["xpred"][ok]).max() <= 1e-7
+    assert (np.abs(out["cost"][ok] - ref["cost"][ok]) <= 1e-8 * np.abs(ref["cost"][ok])).all()
+    assert not out["slack_used"].any() and np.isinf(out["cost"][~ok]).all()
+    prm = dict(MPC_PRM20, N=N, block_size=bs, soft=False)
+    seen_fb = False
+    for b in list(range(24)) + np.nonzero(~ok)[0][:3].tolist():
+        o = mpc_qp.solve_with_ltv(x0[b], xr[b], ur[b], ob[b], **prm)
+        assert (o["status"] == "optimal") == bool(ok[b])
+        assert np.abs(out["u0"][b] - o["optimal_control"]).max() <= 1e-4
+        if ok[b]:
+            assert abs(out["cost"][b] - o["cost"]) <= 1e-6 * abs(o["cost"])
+        else:
+            seen_fb = True
+            sol = mpc.solve_with_ltv(x0[b], xr[b], ur[b], [Obstacle(*r) for r in ob[b]], use_soft_constraints=False)
+            assert sol.status == "fallback" and np.isinf(sol.cost) and not sol.slack_used
+            assert np.allclose(sol.optimal_control, o["optimal_control"])
+    assert seen_fb

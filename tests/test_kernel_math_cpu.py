@@ -197,3 +197,39 @@ def test_emul_mpc_closed_loop_vs_g_mpc(golden):
         x = lin_dare.plant_step(x, u, .02, 2., 3.)
     assert ex < 5e-4 and eu < 5e-3, (ex, eu)
     assert slack == g["slack_ticks"].tolist()
+
+
+@pytest.mark.parametrize("kind,N,bs,M", [(0, 20, 1, 5), (0, 6, 2, 3), (0, 10, 3, 5), (1, 8, 1, 3)])
+def test_emul_mpc_hard_rows_vs_oracle(kind, N, bs, M):
+    """use_soft_constraints=False (mpc_controller.py:197-200, :260-270, :383-386, :464-468): the obstacle rows are
+    hard; an infeasible QP (e.g. the k = 0 row on the fixed initial state violated) gives the fallback solution.
+    The kernel's method of multipliers against the oracle's exact QP solve: same feasible / infeasible verdict,
+    first control 1e-4, objective 1e-6 relative, row violation <= 1e-6, slack_used False."""
+    from hybrid_controller import workloads as wl
+    from hybrid_controller import _native as nat
+    B = 96
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=40 + N, obstacles=wl.DENSE_OBSTACLES[:M])
+    p = nat.mpc_params(kind, N, M, bs, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02, soft=False)
+    out = emul.mpc(p, x0, xr, ur, ob)
+    prm = dict(MPC_PRM20, N=N, block_size=bs, soft=False)
+    n_ok = n_fb = 0
+    for b in range(B):
+        o = (mpc_qp.solve_with_ltv if kind == 0 else mpc_qp.solve)(x0[b], xr[b], ur[b], ob[b], **prm)
+        assert (o["status"] == "optimal") == (out["status"][b] == 0), b
+        assert np.abs(out["u0"][b] - o["optimal_control"]).max() <= 1e-4 and not out["slack_used"][b]
+        if o["status"] == "optimal":
+            n_ok += 1
+            assert abs(out["cost"][b] - o["cost"]) <= 1e-6 * abs(o["cost"])
+            assert np.abs(out["xpred"][b] - o["predicted_states"]).max() <= 1e-5
+            # the rows themselves, on the returned prediction: n.(p_k - o) >= d_safe + r to 1e-6
+            pref = xr[b][:N, :2] if kind == 0 else np.repeat(xr[b][:1, :2], N, 0) * 0 + xr[b][:N, :2]
+            for m in range(M):
+                d = pref - ob[b, m, :2]
+                dist = np.linalg.norm(d, axis=1)
+                keep = dist > 0.01
+                lhs = ((out["xpred"][b][:N, :2] - ob[b, m, :2]) * d).sum(1)[keep] / dist[keep]
+                assert (lhs >= 0.3 + ob[b, m, 2] - 1e-6).all()
+        else:
+            n_fb += 1
+            assert np.isinf(out["cost"][b]) and out["status"][b] == 3
+    assert n_ok >= B // 2 and n_fb >= 1
