@@ -398,7 +398,7 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
     // hard rows: method of multipliers around it -- lm = 0, mu = 2 rho (the soft problem) to start with
     const bool hard = !a.soft && a.M > 0;
     double mu = hard ? 2.0 * a.rho : 0.0, J0 = 0.0, res_prev = 1e300;
-    int outer = 0;
+    int outer = 0, stagnant = 0, softened = 0;
     if (hard) for (int e = 0; e < N * a.M; ++e) SC(a.lam_off + e) = 0.0;
     int cur = 0, it = 0, st = B2C_MAXITER;
     double lamx, lamy, lamt, max_viol = 0.0;
@@ -407,20 +407,23 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
     bool active = true;
     if (infeasible) { st = B2C_INFEASIBLE; active = false; }
     if (!(fabs(J) < 1e300)) { st = B2C_NONFINITE; active = false; }
-    bool need_backward = true;
+    bool need_backward = true, force_outer = false;
     double alpha = 1.0, dec = 0.0;
     int ls = 0;
     while (active) {
         if (need_backward) {
             dec = mpc_backward<BS1>(a, i, cur, lamx, lamy, lamt);
             if (!(dec < 1e300)) { st = B2C_NONFINITE; break; }
-            if (dec <= a.tol * fmax(1.0, fabs(J))) {
+            if (dec <= a.tol * fmax(1.0, fabs(J)) || force_outer) {
+                force_outer = false;
                 if (!hard || max_viol <= MPC_HARD_TOL) { st = B2C_OK; break; }
                 // inner problem solved, rows not yet feasible / complementary: multiplier step.  A residual
                 // that does not drop fourfold asks for a stiffer penalty; no progress at the stiffest means the
                 // rows cannot be met (the reference's solver reports infeasible -> fallback)
-                if (++outer > MPC_HARD_OUTER || (mu >= 1e11 && max_viol > 0.5 * res_prev)) { st = B2C_INFEASIBLE; break; }
-                const bool stiffer = max_viol > 0.25 * res_prev && mu < 1e11;
+                stagnant = (max_viol > 0.9 * res_prev) ? stagnant + 1 : 0;
+                if (stagnant >= 2 && max_viol <= 1e-7) { st = B2C_OK; break; }      // at the rounding floor of the inner solves
+                if (++outer > MPC_HARD_OUTER || (mu >= MPC_HARD_MU_MAX && stagnant >= 5)) { st = B2C_INFEASIBLE; break; }
+                const bool stiffer = max_viol > 0.25 * res_prev && mu < MPC_HARD_MU_MAX;
                 res_prev = max_viol;
                 bool dummy = false;
                 J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, dummy, lamx, lamy, lamt,
@@ -449,7 +452,18 @@ B2C_HD void mpc_solve_one(const MpcArgs& a, const int64_t i) {
             ++ls;
             if (ls == MPC_LS_CLOSED) mpc_gains_to_open_loop<BS1>(a, i);     // the arc continues from this alpha
             if (ls >= MPC_LS_MAX) {               // cannot decrease any further: rounding floor or stall
+                if (hard && dec > 1e-9 * fmax(1.0, fabs(J)) && mu > 2.0 * a.rho && softened < 8) {
+                    // the penalty has become too stiff for the active-set Newton step: back off (any mu is a
+                    // valid method-of-multipliers step; the multipliers are kept) and carry on from this point
+                    mu *= 0.1; ++softened; res_prev = 1e300;
+                    bool dm = false;
+                    J = mpc_forward<BS1, false>(a, i, z0x, z0y, z0t, cur, cur, 0.0, max_viol, dm, lamx, lamy, lamt,
+                                                mu, false, &J0);
+                    need_backward = true;
+                    continue;
+                }
                 st = (dec <= 1e-9 * fmax(1.0, fabs(J))) ? B2C_OK : B2C_MAXITER;
+                if (st == B2C_OK && hard && max_viol > MPC_HARD_TOL) { need_backward = true; dec = 0.0; st = B2C_MAXITER; force_outer = true; continue; }
                 break;
             }
         }

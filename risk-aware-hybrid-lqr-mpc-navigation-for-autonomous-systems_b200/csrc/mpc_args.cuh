@@ -43,7 +43,7 @@ static inline void mpc_fill_args(MpcArgs& a, int64_t B, const b2c_mpc_params* p,
     a.B = B; a.kind = p->kind; a.N = p->N; a.M = p->M;
     a.bs = (p->kind == B2C_MPC_LTV && p->block_size > 1) ? p->block_size : 1;
     a.Nb = (a.N + a.bs - 1) / a.bs;
-    a.max_iter = p->max_iter > 0 ? p->max_iter : ((p->soft || p->M == 0) ? 60 : 600);   // hard rows: all multiplier rounds together
+    a.max_iter = p->max_iter > 0 ? p->max_iter : ((p->soft || p->M == 0) ? 60 : 2000);   // hard rows: all multiplier rounds together
     a.ramp_up_steps = p->ramp_up_steps; a.soft = p->soft;
     a.q0 = p->Qd[0]; a.q1 = p->Qd[1]; a.q2 = p->Qd[2]; a.r0 = p->Rd[0]; a.r1 = p->Rd[1];
     a.p0 = p->Pd[0]; a.p1 = p->Pd[1]; a.p2 = p->Pd[2];
@@ -61,7 +61,8 @@ int  mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb);
 #define MPC_LS_CLOSED 3    // closed-loop trials (alpha = 1, 1/2, 1/4) before the projection arc
 #define MPC_LS_MAX 18
 #define MPC_HARD_TOL 1e-9    // hard rows: KKT residual (violation / complementarity, metres) at which the multiplier loop stops
-#define MPC_HARD_OUTER 60    // multiplier updates before the rows are declared infeasible
+#define MPC_HARD_OUTER 120   // multiplier updates before the rows are declared infeasible
+#define MPC_HARD_MU_MAX 1e6  // stiffest penalty tried (beyond it the piecewise-quadratic inner problem chatters)
 // First trial step of a Newton iteration: min(1, MPC_LS_GROW * the step the previous iteration accepted).
 // Full steps stay full (quadratic convergence is untouched: after an accepted alpha = 1 the next trial is 1);
 // an instance that is crossing kinks of the obstacle penalty, where only alpha ~ 1/64 descends, no longer
