@@ -431,6 +431,7 @@ def test_mpc_hard_rows_vs_oracle_and_emulation(hc, N, bs, M):
     the same code, a subset against the oracle's exact QP, and the scalar drop-in call incl. an infeasible instance
     (status "fallback", cost inf, as the reference returns when its solver reports infeasible)."""
     import emul
+    from oracle import mpc_qp
     from hybrid_controller.controllers.mpc_controller import MPCController, Obstacle
     from hybrid_controller import workloads as wl, _native as nat
     B = 2048
