@@ -583,7 +583,7 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     int tpb = 0;
     const bool slots_ok = mpc_slots_eligible(a, &tpb);
     if (p->engine == B2C_MPC_ENGINE_SLOTS && !slots_ok) {
-        b2c_set_error("slot kernel needs kind=LTV, block_size=1, soft rows and 10N+3M <= 895");
+        b2c_set_error("slot kernel needs kind=LTV, block_size=1, soft rows and 10N+3M <= 896");
         return -5;
     }
     if (slots_ok && p->engine != B2C_MPC_ENGINE_GENERAL) return mpc_slots_launch(ctx, a, tpb);

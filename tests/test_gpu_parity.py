@@ -459,3 +459,28 @@ def test_mpc_hard_rows_vs_oracle_and_emulation(hc, N, bs, M):
             assert sol.status == "fallback" and np.isinf(sol.cost) and not sol.slack_used
             assert np.allclose(sol.optimal_control, o["optimal_control"])
     assert seen_fb
+
+
+@pytest.mark.gpu
+def test_mpc_lti_hard_rows_scalar_api(hc):
+    """MPCController.solve (LTI, absolute state, padded references) with use_soft_constraints=False through the
+    drop-in class, against the oracle's exact QP; both verdicts occur."""
+    from oracle import mpc_qp
+    from hybrid_controller.controllers.mpc_controller import MPCController, Obstacle
+    from hybrid_controller import workloads as wl
+    N, M = 8, 3
+    x0, xr, ur, ob = wl.config4_instances(40, N=N, seed=9, obstacles=wl.DEFAULT_OBSTACLES)
+    mpc = MPCController(horizon=N, **wl.SIM_MPC)
+    prm = dict(MPC_PRM20, N=N, block_size=1, soft=False)
+    verdicts = set()
+    for b in range(40):
+        obs = [Obstacle(*r) for r in ob[b]]
+        sol = mpc.solve(x0[b], xr[b][:5], ur[b][:4], obs, use_soft_constraints=False)      # short refs: padded, :172-183
+        o = mpc_qp.solve(x0[b], xr[b][:5], ur[b][:4], ob[b], **prm)
+        assert sol.status == o["status"] and not sol.slack_used
+        verdicts.add(sol.status)
+        assert np.abs(sol.optimal_control - o["optimal_control"]).max() <= 1e-4
+        if sol.status == "optimal":
+            assert abs(sol.cost - o["cost"]) <= 1e-6 * abs(o["cost"])
+            assert np.abs(sol.predicted_states - o["predicted_states"]).max() <= 1e-5
+    assert verdicts == {"optimal", "fallback"}

@@ -94,3 +94,16 @@ def test_rollout_is_sharding_invariant_and_log_free_path():
     for key in ("x", "lqr_steps", "mpc_solves", "switches", "collision_states", "mean_error", "final_error"):
         assert np.array_equal(full[key], np.concatenate([a[key], b[key]])), key
     assert np.array_equal(a["states"][:, -1], a["x"])
+
+
+def test_rollout_without_obstacles_and_single_robot():
+    """No obstacles: the risk is 0, the hybrid loop never leaves LQR and equals the LQR loop; R = 1 works."""
+    from hybrid_controller.rollout import simulate_batch
+    lqr, mpc, risk = _controllers()
+    table = lin_dare.figure8(20.0)
+    x0 = table[5:6, 1:4] + 0.03
+    a = simulate_batch("hybrid", table, [5], x0, np.zeros((0, 3)), 200, lqr=lqr, mpc=mpc, risk=risk, log=True)
+    b = simulate_batch("lqr", table, [5], x0, np.zeros((0, 3)), 200, lqr=lqr, log=True)
+    assert a["mpc_solves"][0] == 0 and a["switches"][0] == 0 and a["lqr_steps"][0] == 200
+    assert np.array_equal(a["states"], b["states"]) and np.array_equal(a["controls"], b["controls"])
+    assert (a["risk"] == 0).all() and a["collision_states"][0] == 0
