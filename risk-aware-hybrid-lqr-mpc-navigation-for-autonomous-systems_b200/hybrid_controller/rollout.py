@@ -61,7 +61,7 @@ def simulate_batch(mode: str, table, k0, x0, obstacles, ticks: int, lqr=None, mp
         obstacles = np.broadcast_to(obstacles[None], (R,) + obstacles.shape)
     M = obstacles.shape[1] if obstacles.size else 0
     p = rollout_params(mode, ticks, table.shape[0], lqr, mpc, risk, M, dt, plant_v_max, plant_w_max, mpc_rate, min_dwell)
-    x = np.ascontiguousarray(x0.T)                                   # [3][R]
+    x = np.array(x0.T, dtype=np.float64, order="C", copy=True)       # [3][R]; a copy even when R == 1 (the caller's x0 stays untouched)
     ob = np.ascontiguousarray(obstacles.reshape(R, 3 * M).T) if M else np.zeros((1, R))
     sc = None if mpc_step_count is None else np.ascontiguousarray(mpc_step_count, np.int32).copy()
     counters, stats = np.zeros((5, R), np.int32), np.zeros((3, R))
