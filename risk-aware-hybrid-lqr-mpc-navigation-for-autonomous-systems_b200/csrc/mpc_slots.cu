@@ -96,6 +96,7 @@ struct SlotState {
     double alpha, J, dec, z0x, z0y, z0t, lamx, lamy, lamt, max_viol;
     double x0x, x0t, r0x, r0t;                        // kept for the fallback law
     double ur00, ur01;                                // first reference input (outputs)
+    int rej;                                          // a trial step of this solve has been rejected (kernel: asks for helper lanes)
 };
 
 // ----- setup: claim instance i, stage its constants, w = clip(0) ---------------------------------
@@ -138,7 +139,7 @@ template <int SS, int MT>
 B2C_HD void setup_owner(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_t i) {
     const int N = a.N, M = (MT >= 0) ? MT : a.M;
     const int64_t B = a.B;
-    s.inst = i; s.it = 0; s.ls = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
+    s.inst = i; s.it = 0; s.ls = 0; s.rej = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
     const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + B + i), x0t = B2C_LDG(a.x0 + 2 * B + i);
     const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + B + i), r0t = B2C_LDG(a.xref + 2 * B + i);
     for (int e = 0; e < M; ++e) {                 // obstacle strip: x, y, d_safe + r
@@ -370,6 +371,29 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     return dec;
 }
 
+// gains in U -> the OPEN-LOOP Newton direction of the linear model (K = 0, kf = -d)
+template <int SS>
+B2C_HD void slot_open_loop(const MpcArgs& a, const SlotMem& m) {
+    const int N = a.N;
+    double dx = 0.0, dy = 0.0, dth = 0.0;
+    double ck, sk, uo0, uo1;
+    g_load4(m, 0, ck, sk, uo0, uo1);
+    for (int j = 0; j < N; ++j) {
+        double nck, nsk, nuo0;
+        g_load4(m, (j + 1 < N) ? (j + 1) : j, nck, nsk, nuo0, uo1);
+        const double d0 = -MU(8 * j + 6) - (MU(8 * j + 0) * dx + MU(8 * j + 1) * dy + MU(8 * j + 2) * dth);
+        const double d1 = -MU(8 * j + 7) - (MU(8 * j + 3) * dx + MU(8 * j + 4) * dy + MU(8 * j + 5) * dth);
+        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
+        const double ndx = dx + (-vr * sk) * dth + ck * d0;
+        const double ndy = dy + (vr * ck) * dth + sk * d0;
+        dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+#pragma unroll
+        for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
+        MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
+        ck = nck; sk = nsk; uo0 = nuo0;
+    }
+}
+
 // ----- undo a rejected trial -------------------------------------------------------------------------
 // W <- parked previous inputs; U <- gains from the mirror (independent loads, unrolled so they overlap).
 // From the MPC_LS_CLOSED-th rejection of an iteration on, the gains are then rewritten as the OPEN-LOOP
@@ -388,24 +412,7 @@ B2C_HD void slot_restore(const MpcArgs& a, const SlotMem& m, const bool open_loo
         MU(8 * j + 3) = q1.y; MU(8 * j + 4) = q2.x; MU(8 * j + 5) = q2.y;
         MU(8 * j + 6) = q3.x; MU(8 * j + 7) = q3.y;
     }
-    if (!open_loop) return;
-    double dx = 0.0, dy = 0.0, dth = 0.0;
-    double ck, sk, uo0, uo1;
-    g_load4(m, 0, ck, sk, uo0, uo1);
-    for (int j = 0; j < N; ++j) {
-        double nck, nsk, nuo0;
-        g_load4(m, (j + 1 < N) ? (j + 1) : j, nck, nsk, nuo0, uo1);
-        const double d0 = -MU(8 * j + 6) - (MU(8 * j + 0) * dx + MU(8 * j + 1) * dy + MU(8 * j + 2) * dth);
-        const double d1 = -MU(8 * j + 7) - (MU(8 * j + 3) * dx + MU(8 * j + 4) * dy + MU(8 * j + 5) * dth);
-        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
-        const double ndx = dx + (-vr * sk) * dth + ck * d0;
-        const double ndy = dy + (vr * ck) * dth + sk * d0;
-        dth = dth + a.dt * d1; dx = ndx; dy = ndy;
-#pragma unroll
-        for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
-        MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
-        ck = nck; sk = nsk; uo0 = nuo0;
-    }
+    if (open_loop) slot_open_loop<SS>(a, m);
 }
 
 // ----- outputs (:484-522 on success, _get_fallback_solution :316-343 otherwise) -----------------------
@@ -486,11 +493,13 @@ B2C_HD void slot_phase_backward(const MpcArgs& a, const SlotMem& m, SlotState& s
     ++s.it; s.ls = 0; s.mode = SLOT_FWD_GAIN;
 }
 
+// what follows a forward sweep.  `krej`: trial steps rejected together when this one is (1 on the host and for a
+// lane working alone; 1 + helpers when idle lanes of the warp evaluated the next shorter steps in the same
+// round -- the state reached is the one krej successive rejections reach: alpha halves krej times, the
+// restore is idempotent).
 template <int SS, int MT>
-B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
-    double mv, lx, ly, lt;
-    const bool gain = (s.mode == SLOT_FWD_GAIN);
-    const double Jn = slot_forward<SS, MT>(a, m, s, gain, mv, lx, ly, lt);
+B2C_HD void slot_forward_post(const MpcArgs& a, const SlotMem& m, SlotState& s, const bool gain, const double Jn,
+                              const double mv, const double lx, const double ly, const double lt, const int krej) {
     if (!gain) {                                  // first evaluation of a fresh instance
         s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;
         if (!(a.v_max >= 0.0) || !(a.w_max >= 0.0)) { s.st = B2C_INFEASIBLE; slot_finish<SS, MT>(a, m, s); return; }
@@ -502,12 +511,21 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
         s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt; s.mode = SLOT_BWD;
         return;
     }
-    s.alpha *= 0.5; ++s.ls;                       // reject: undo, shorten (the arc continues from this alpha)
+    for (int r = 0; r < krej; ++r) s.alpha *= 0.5;    // reject: undo, shorten (the arc continues from this alpha)
+    s.ls += krej; s.rej = 1;
     slot_restore<SS, MT>(a, m, s.ls >= MPC_LS_CLOSED);
     if (s.ls >= MPC_LS_MAX) {                     // rounding floor or stall
         s.st = (s.dec <= 1e-9 * fmax(1.0, fabs(s.J))) ? B2C_OK : B2C_MAXITER;
         slot_finish<SS, MT>(a, m, s);
     }
+}
+
+template <int SS, int MT>
+B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s) {
+    double mv, lx, ly, lt;
+    const bool gain = (s.mode == SLOT_FWD_GAIN);
+    const double Jn = slot_forward<SS, MT>(a, m, s, gain, mv, lx, ly, lt);
+    slot_forward_post<SS, MT>(a, m, s, gain, Jn, mv, lx, ly, lt, 1);
 }
 
 // ----- difficulty classes (work ordering only; never changes a result) ------------------------------
@@ -570,29 +588,47 @@ __device__ __forceinline__ unsigned long long trace_ns() {
 #else
 #define TRACE(...)
 #endif
+// Helper lanes (the tail of a batch).  The kernel's makespan at BASELINE's batch size is the latency of its
+// hardest instances: 13 Newton iterations plus as many rejected trial steps, one forward sweep each.  An instance
+// that has had a trial rejected (s.rej) therefore keeps up to MPC_SPEC_HELPERS idle lanes of its warp from
+// refilling while the queue is short (remaining <= MPC_SPEC_TAIL x resident slots), and those lanes evaluate the
+// NEXT trial steps of the same iteration (alpha/2, alpha/4, ...) in the same round, on copies of the owner's strips.
+// The first trial of the sequence that decreases the cost is taken -- the sequence and every sweep are those of
+// the sequential line search, so results do not depend on whether, or how many, helpers were there.  If the winner
+// is a helper, the instance simply continues on that lane (state by shuffle, the two lanes swap global strips).
+#ifndef MPC_SPEC_HELPERS
+#define MPC_SPEC_HELPERS 3
+#endif
+#ifndef MPC_SPEC_TAIL
+#define MPC_SPEC_TAIL 4
+#endif
 template <int SS, int MT>
 __global__ void __launch_bounds__(SS, 1)
 k_mpc_slots(const MpcArgs a) {
     extern __shared__ double smem[];
     constexpr int tpb = SS;
     const int lane = threadIdx.x & 31;
-    const int64_t slot = (int64_t)blockIdx.x * tpb + threadIdx.x;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int64_t strip = (int64_t)blockIdx.x * tpb + threadIdx.x;  // global strip this lane's instance uses (moves with it)
+    double* const gg_base = a.scratch + (int64_t)6 * a.N * a.nslots;
     SlotMem m;
     m.w = smem + threadIdx.x;
     m.u = m.w + (size_t)2 * a.N * tpb;
     m.ob = m.u + (size_t)8 * a.N * tpb;
     m.ring = smem + (size_t)slot_fields(a) * tpb + (size_t)threadIdx.x * 6;
     m.gs = a.nslots;
-    m.g = a.scratch + slot * 6;
-    m.gg = a.scratch + (int64_t)6 * a.N * a.nslots + slot * 8;
+    m.g = a.scratch + strip * 6;
+    m.gg = gg_base + strip * 8;
     SlotState s;
-    s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0;
+    s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0; s.rej = 0;
     s.alpha = s.J = s.dec = s.z0x = s.z0y = s.z0t = s.lamx = s.lamy = s.lamt = s.max_viol = 0.0;
     s.x0x = s.x0t = s.r0x = s.r0t = s.ur00 = s.ur01 = 0.0;
     bool empty = false;
     const unsigned FULL = 0xffffffffu;
     unsigned long long cum0 = 0, cum1 = 0, cum2 = 0;          // class boundaries in queue order
     if (a.perm) { cum0 = a.class_count[0]; cum1 = cum0 + a.class_count[1]; cum2 = cum1 + a.class_count[2]; }
+    int64_t seen = 0;                                         // queue position at this warp's last claim
+    const int nfields = slot_fields(a);
     TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;
           long long tr_x0 = 0, tr_x1 = 0, tr_x2 = 0, tr_x3 = 0, tr_x4 = 0, tr_x5 = 0;)
     for (;;) {
@@ -600,17 +636,23 @@ k_mpc_slots(const MpcArgs a) {
         if (s.mode == SLOT_BWD) slot_phase_backward<SS, MT>(a, m, s);
         __syncwarp();
         TRACE(tr_b += clock64() - tr_c; tr_c = clock64();)
-        const bool want = (s.mode == SLOT_IDLE) && !empty;
+        // lanes kept back as helpers: MPC_SPEC_HELPERS per instance with a rejected trial behind it, near the tail only
+        const unsigned idle0 = __ballot_sync(FULL, s.mode == SLOT_IDLE);
+        const unsigned req_m = __ballot_sync(FULL, s.mode == SLOT_FWD_GAIN && s.rej);
+        int keep = 0;
+        if (req_m && (a.B - seen) <= (int64_t)MPC_SPEC_TAIL * a.nslots) keep = MPC_SPEC_HELPERS * __popc(req_m);
+        const bool want = (s.mode == SLOT_IDLE) && !empty && (__popc(idle0 & lt_mask) < __popc(idle0) - keep);
         const unsigned need = __ballot_sync(FULL, want);
         if (need) {
             const int leader = __ffs(need) - 1;
             unsigned long long base = 0;
             if (lane == leader) base = atomicAdd(a.queue, (unsigned long long)__popc(need));
             base = __shfl_sync(FULL, base, leader);
+            seen = (int64_t)base + __popc(need);
             int64_t id = 0;
             bool id_ok = false;
             if (want) {
-                id = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                id = (int64_t)base + __popc(need & lt_mask);
                 if (id < a.B) {
                     id_ok = true;
                     if (a.perm) {                             // queue position -> (class, offset) -> instance
@@ -668,9 +710,10 @@ k_mpc_slots(const MpcArgs a) {
                 k = lane / cnt; n = lane - k * cnt;
                 for (int t = lane; t - lane < T; t += 32) {
                     const int tl = __shfl_sync(FULL, nth, n);
+                    const int64_t tstrip = __shfl_sync(FULL, strip, tl);
                     if (t < T) {
                         SlotMem tm = m;
-                        tm.w += tl - lane; tm.u += tl - lane; tm.g += (int64_t)(tl - lane) * 6;
+                        tm.w += tl - lane; tm.u += tl - lane; tm.g = a.scratch + tstrip * 6;
                         setup_stage<SS>(a, tm, k);
                     }
                     k += dk; n += dn;
@@ -683,7 +726,85 @@ k_mpc_slots(const MpcArgs a) {
         if (empty && __all_sync(FULL, s.mode == SLOT_IDLE)) break;
         __syncwarp();
         TRACE(tr_r += clock64() - tr_c; tr_c = clock64();)
-        if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) slot_phase_forward<SS, MT>(a, m, s);
+        // ---- forward phase: every lane with a sweep to run, plus the idle lanes lent to requesting instances
+        const bool gain = (s.mode == SLOT_FWD_GAIN);
+        const unsigned idle_m = __ballot_sync(FULL, s.mode == SLOT_IDLE);
+        const bool team_round = (idle_m != 0u) && (req_m != 0u);          // warp-uniform
+        int ol = lane, off = 0, ols = 0;                                  // team owner, trial offset, owner's trial index
+        bool helper = false;
+        SlotState fs = s;
+        SlotMem mf = m;
+        double Jref = s.J;
+        if (team_round) {
+            const int nown = __popc(req_m);
+            const int ir = __popc(idle_m & lt_mask);
+            const int cand = __fns(req_m, 0, (ir % nown) + 1);
+            const int coff = 1 + ir / nown;
+            ols = __shfl_sync(FULL, s.ls, cand);
+            helper = (s.mode == SLOT_IDLE) && (ols + coff <= MPC_LS_MAX - 1);
+            if (helper) { ol = cand; off = coff; }
+            const double oz0x = __shfl_sync(FULL, s.z0x, ol), oz0y = __shfl_sync(FULL, s.z0y, ol);
+            const double oz0t = __shfl_sync(FULL, s.z0t, ol), oal = __shfl_sync(FULL, s.alpha, ol);
+            const double oJ = __shfl_sync(FULL, s.J, ol);
+            const int64_t ostrip = __shfl_sync(FULL, strip, ol);
+            if (helper) {
+                fs.z0x = oz0x; fs.z0y = oz0y; fs.z0t = oz0t; Jref = oJ;
+                double al = oal;
+                for (int r = 0; r < off; ++r) al *= 0.5;
+                fs.alpha = al;
+                mf.g = a.scratch + ostrip * 6;
+                const int d = ol - lane;                                  // the owner's strips (W, U, OB) -> mine
+                for (int f = 0; f < nfields; ++f) m.w[(size_t)f * SS] = m.w[(size_t)f * SS + d];
+                if (ols < MPC_LS_CLOSED && ols + off >= MPC_LS_CLOSED) slot_open_loop<SS>(a, mf);
+            }
+            __syncwarp();
+        }
+        const bool run = gain || (s.mode == SLOT_FWD_PLAIN) || helper;
+        const bool fgain = gain || helper;
+        double Jn = 0.0, mv = 0.0, lx = 0.0, ly = 0.0, lt = 0.0;
+        if (run) Jn = slot_forward<SS, MT>(a, mf, fs, fgain, mv, lx, ly, lt);
+        __syncwarp();
+        int krej = 1;
+        bool handled = false;                                             // my instance moved to a helper's lane
+        if (team_round) {
+            const unsigned okb = __ballot_sync(FULL, run && fgain && (Jn < Jref));
+            const unsigned team = __match_any_sync(FULL, ol);
+            const unsigned tok = team & okb;
+            int win = -1;                                                 // lane whose trial is taken
+            if (tok & (1u << ol)) win = ol;
+            else if (tok) win = __ffs(tok) - 1;                           // helpers: offsets ascend with the lane number
+            krej = __popc(team);
+            const bool moved = (win >= 0 && win != ol);
+            if (__any_sync(FULL, moved)) {
+                const int src = (moved && lane == win) ? ol : lane;       // new owner reads the old owner's state
+                const int par = moved ? ((lane == win) ? ol : ((lane == ol) ? win : lane)) : lane;
+                const int64_t pstrip = __shfl_sync(FULL, strip, par);
+                SlotState t;
+                t.inst = __shfl_sync(FULL, s.inst, src);
+                t.it = __shfl_sync(FULL, s.it, src); t.st = __shfl_sync(FULL, s.st, src);
+                t.dec = __shfl_sync(FULL, s.dec, src);
+                t.z0x = __shfl_sync(FULL, s.z0x, src); t.z0y = __shfl_sync(FULL, s.z0y, src); t.z0t = __shfl_sync(FULL, s.z0t, src);
+                t.x0x = __shfl_sync(FULL, s.x0x, src); t.x0t = __shfl_sync(FULL, s.x0t, src);
+                t.r0x = __shfl_sync(FULL, s.r0x, src); t.r0t = __shfl_sync(FULL, s.r0t, src);
+                t.ur00 = __shfl_sync(FULL, s.ur00, src); t.ur01 = __shfl_sync(FULL, s.ur01, src);
+                if (moved && lane == win) {                               // I take the instance over, trial accepted
+                    s.inst = t.inst; s.it = t.it; s.st = t.st; s.dec = t.dec;
+                    s.z0x = t.z0x; s.z0y = t.z0y; s.z0t = t.z0t; s.x0x = t.x0x; s.x0t = t.x0t; s.r0x = t.r0x; s.r0t = t.r0t;
+                    s.ur00 = t.ur00; s.ur01 = t.ur01;
+                    s.alpha = fs.alpha; s.ls = ols + off; s.rej = 1;
+                    s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;
+                    s.mode = SLOT_BWD;
+                    strip = pstrip;
+                } else if (moved && lane == ol) {                         // my instance went to lane `win`
+                    s.mode = SLOT_IDLE; s.inst = -1; s.rej = 0;
+                    strip = pstrip;
+                    handled = true;
+                }
+                m.g = a.scratch + strip * 6;
+                m.gg = gg_base + strip * 8;
+            }
+        }
+        if (!handled && !helper && run) slot_forward_post<SS, MT>(a, m, s, gain, Jn, mv, lx, ly, lt, krej);
         __syncwarp();
         TRACE(tr_f += clock64() - tr_c;)
     }
