@@ -371,26 +371,32 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     return dec;
 }
 
-// gains in U -> the OPEN-LOOP Newton direction of the linear model (K = 0, kf = -d)
+// gains in U -> the OPEN-LOOP Newton direction of the linear model (K = 0, kf = -d).  The stage constants come from
+// the global strip four stages at a time (one L2 round trip per four stages instead of one per stage).
 template <int SS>
 B2C_HD void slot_open_loop(const MpcArgs& a, const SlotMem& m) {
     const int N = a.N;
+    constexpr int C = 4;
     double dx = 0.0, dy = 0.0, dth = 0.0;
-    double ck, sk, uo0, uo1;
-    g_load4(m, 0, ck, sk, uo0, uo1);
-    for (int j = 0; j < N; ++j) {
-        double nck, nsk, nuo0;
-        g_load4(m, (j + 1 < N) ? (j + 1) : j, nck, nsk, nuo0, uo1);
-        const double d0 = -MU(8 * j + 6) - (MU(8 * j + 0) * dx + MU(8 * j + 1) * dy + MU(8 * j + 2) * dth);
-        const double d1 = -MU(8 * j + 7) - (MU(8 * j + 3) * dx + MU(8 * j + 4) * dy + MU(8 * j + 5) * dth);
-        const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
-        const double ndx = dx + (-vr * sk) * dth + ck * d0;
-        const double ndy = dy + (vr * ck) * dth + sk * d0;
-        dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+    for (int j0 = 0; j0 < N; j0 += C) {
+        double ck[C], sk[C], uo0[C], uo1[C];
 #pragma unroll
-        for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
-        MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
-        ck = nck; sk = nsk; uo0 = nuo0;
+        for (int c = 0; c < C; ++c) g_load4(m, (j0 + c < N) ? (j0 + c) : (N - 1), ck[c], sk[c], uo0[c], uo1[c]);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const int j = j0 + c;
+            if (j < N) {
+                const double d0 = -MU(8 * j + 6) - (MU(8 * j + 0) * dx + MU(8 * j + 1) * dy + MU(8 * j + 2) * dth);
+                const double d1 = -MU(8 * j + 7) - (MU(8 * j + 3) * dx + MU(8 * j + 4) * dy + MU(8 * j + 5) * dth);
+                const double vr = b2c_guard_v(uo0[c], B2C_GUARD_MPC);
+                const double ndx = dx + (-vr * sk[c]) * dth + ck[c] * d0;
+                const double ndy = dy + (vr * ck[c]) * dth + sk[c] * d0;
+                dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+#pragma unroll
+                for (int e = 0; e < 6; ++e) MU(8 * j + e) = 0.0;
+                MU(8 * j + 6) = -d0; MU(8 * j + 7) = -d1;
+            }
+        }
     }
 }
 
@@ -754,7 +760,15 @@ k_mpc_slots(const MpcArgs a) {
                 fs.alpha = al;
                 mf.g = a.scratch + ostrip * 6;
                 const int d = ol - lane;                                  // the owner's strips (W, U, OB) -> mine
-                for (int f = 0; f < nfields; ++f) m.w[(size_t)f * SS] = m.w[(size_t)f * SS + d];
+                int f = 0;                                                // eight loads in flight per store batch
+                for (; f + 8 <= nfields; f += 8) {
+                    double t8[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) t8[e] = m.w[(size_t)(f + e) * SS + d];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) m.w[(size_t)(f + e) * SS] = t8[e];
+                }
+                for (; f < nfields; ++f) m.w[(size_t)f * SS] = m.w[(size_t)f * SS + d];
                 if (ols < MPC_LS_CLOSED && ols + off >= MPC_LS_CLOSED) slot_open_loop<SS>(a, mf);
             }
             __syncwarp();
