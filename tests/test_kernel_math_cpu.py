@@ -100,7 +100,8 @@ def test_emul_slot_state_machine_vs_oracle_and_general(N, M):
     gen = emul.mpc(_params(N, M, 1), x0, xr, ur, ob, step_count=sc)
     assert np.array_equal(out["status"], gen["status"]) and out["status"][5] != 0 and (out["status"] != 0).sum() == 1
     assert np.array_equal(out["iters"], gen["iters"]) and np.array_equal(out["step_count"], gen["step_count"])
-    assert np.isinf(out["cost"][5]) and np.array_equal(out["u0"][5], gen["u0"][5])
+    # NaN input: the fallback law clips NaN to NaN, as np.clip does in the reference (mpc_controller.py:554-559)
+    assert np.isinf(out["cost"][5]) and np.array_equal(out["u0"][5], gen["u0"][5], equal_nan=True) and np.isnan(out["u0"][5, 0])
     prm = dict(MPC_PRM20, N=N, block_size=1)
     for b in range(B):
         if b == 5:
