@@ -25,6 +25,7 @@ namespace {
 struct SlotMem {
     double* w;  double* u;  double* ob;               // shared strips, element (f) at f*SS (host emulation: SS = 1)
     double* ring;                                     // this lane's cell of ring slot 0 (device only)
+    double* ring4;                                    // the same memory as a three-stage ring of four (backward sweep)
     double* g;  double* gg; int64_t gs;               // global strips: stage k of this slot at g + k*6*gs / gg + k*8*gs
 };
 // 16-byte vector access to the global strips (6 resp. 8 contiguous doubles per stage and slot)
@@ -55,14 +56,14 @@ B2C_HD void gg_store(const SlotMem& m, int j, double K00, double K01, double K02
 
 // Two-stage ring in shared memory for the read-only stage constants: stage k+2 is fetched with
 // cp.async (LDGSTS, no register dependency) while stages k and k+1 are being computed, so the L2
-// latency of the G strip never reaches the recursion.  Cell of lane l, ring slot r: ring[(r*SS + l)*6 .. +6).
+// latency of the G strip never reaches the recursion.  Cell of lane l, ring slot r, in the warp's block: [(r*32 + l)*6 .. +6).
 // `dep` is a value computed from the cell being overwritten: it orders the refill after the read.
 template <int SS>
 B2C_HD void ring_issue(const SlotMem& m, int k, bool valid, double dep) {
 #ifdef __CUDA_ARCH__
     if (valid) {
         const double* src = m.g + (int64_t)k * 6 * m.gs;
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(m.ring + (size_t)(k & 1) * 6 * SS);
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(m.ring + (size_t)(k & 1) * 6 * 32);
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\t"
                      "cp.async.cg.shared.global [%0+16], [%1+16], 16;\n\t"
                      "cp.async.cg.shared.global [%0+32], [%1+32], 16;  // after %2"
@@ -77,11 +78,43 @@ template <int SS>
 B2C_HD Stage6 ring_take(const SlotMem& m, int k) {
 #ifdef __CUDA_ARCH__
     asm volatile("cp.async.wait_group 1;" ::: "memory");
-    const double2* p = reinterpret_cast<const double2*>(m.ring + (size_t)(k & 1) * 6 * SS);
+    const double2* p = reinterpret_cast<const double2*>(m.ring + (size_t)(k & 1) * 6 * 32);
     const double2 a = p[0], b = p[1], c = p[2];
     return Stage6{a.x, a.y, b.x, b.y, c.x, c.y};
 #else
     return g_load(m, k);
+#endif
+}
+
+// The backward sweep needs four of the six constants (cos*dt, sin*dt, u_ref) and its stages are the short ones
+// (600 cycles against an L2 round trip that can exceed 1,200 under load): the same 12 doubles per slot then hold a
+// THREE-stage ring of four, stage j-3 fetched while j .. j-2 are computed.  Cell of lane l, ring slot r, in the
+// warp's block: [(r*32 + l)*4 .. +4).
+template <int SS>
+B2C_HD void ringb_issue(const SlotMem& m, int k, int r, bool valid, double dep) {
+#ifdef __CUDA_ARCH__
+    if (valid) {
+        const double* src = m.g + (int64_t)k * 6 * m.gs;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(m.ring4 + (size_t)r * 4 * 32);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\t"
+                     "cp.async.cg.shared.global [%0+16], [%1+16], 16;  // after %2"
+                     :: "r"(dst), "l"(src), "d"(dep) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#else
+    (void)m; (void)k; (void)r; (void)valid; (void)dep;
+#endif
+}
+template <int SS>
+B2C_HD void ringb_take(const SlotMem& m, int k, int r, double& ck, double& sk, double& uo0, double& uo1) {
+#ifdef __CUDA_ARCH__
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    const double2* p = reinterpret_cast<const double2*>(m.ring4 + (size_t)r * 4 * 32);
+    const double2 a = p[0], b = p[1];
+    ck = a.x; sk = a.y; uo0 = b.x; uo1 = b.y;
+#else
+    (void)r;
+    g_load4(m, k, ck, sk, uo0, uo1);
 #endif
 }
 
@@ -314,13 +347,16 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     // the mirror store of stage j+1 is issued one stage late, from registers nothing else wants in between
     // (issued in place, the next writes to its source registers stalled on the store queue)
     double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0, p4 = 0.0, p5 = 0.0, p6 = 0.0, p7 = 0.0;
-    ring_issue<SS>(m, N - 1, true, 0.0);
-    ring_issue<SS>(m, N - 2, N > 1, 0.0);
+    ringb_issue<SS>(m, N - 1, 0, true, 0.0);
+    ringb_issue<SS>(m, N - 2, 1, N > 1, 0.0);
+    ringb_issue<SS>(m, N - 3, 2, N > 2, 0.0);
+    int rs = 0;                                       // ring slot of stage j
     for (int j = N - 1; j >= 0; --j) {
         if (j < N - 1) gg_store(m, j + 1, p0, p1, p2, p3, p4, p5, p6, p7);
-        const Stage6 cur = ring_take<SS>(m, j);
-        const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1;
-        ring_issue<SS>(m, j - 2, j >= 2, ck + cur.pry);      // constants two stages ahead
+        double ck, sk, uo0, uo1;
+        ringb_take<SS>(m, j, rs, ck, sk, uo0, uo1);
+        ringb_issue<SS>(m, j - 3, rs, j >= 3, ck + uo1);     // constants three stages ahead, into the cell just read
+        rs = (rs == 2) ? 0 : rs + 1;
         const double gz0 = MU(8 * j + 0), gz1 = MU(8 * j + 1), gz2 = MU(8 * j + 2);
         const double H0 = MU(8 * j + 3), H1 = MU(8 * j + 4), H3 = MU(8 * j + 5);
         const double w0 = MW(2 * j), w1 = MW(2 * j + 1);
@@ -630,7 +666,11 @@ k_mpc_slots(const MpcArgs a) {
     m.w = smem + threadIdx.x;
     m.u = m.w + (size_t)2 * a.N * tpb;
     m.ob = m.u + (size_t)8 * a.N * tpb;
-    m.ring = smem + (size_t)slot_fields(a) * tpb + (size_t)threadIdx.x * 6;
+    // ring memory: 12 x 32 doubles per WARP (the two layouts below overlap inside a warp's block only -- warps are not
+    // synchronised with each other, a warp's own phases are)
+    double* const wring = smem + (size_t)slot_fields(a) * tpb + (size_t)(threadIdx.x >> 5) * 384;
+    m.ring = wring + (size_t)lane * 6;                        // forward: 2 stages x [32 lanes][6]
+    m.ring4 = wring + (size_t)lane * 4;                       // backward: 3 stages x [32 lanes][4]
     m.gs = a.nslots;
     m.g = a.scratch + strip * 6;
     m.gg = gg_base + strip * 8;
@@ -929,7 +969,7 @@ extern "C" int b2c_emul_mpc_slots(int64_t B, const b2c_mpc_params* p,
     if (!mpc_slots_eligible(a, &tpb)) return -5;
     std::vector<double> sm((size_t)slot_fields(a)), gl((size_t)14 * a.N);
     SlotMem m;
-    m.ring = nullptr; m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
+    m.ring = nullptr; m.ring4 = nullptr; m.w = sm.data(); m.u = m.w + 2 * a.N; m.ob = m.u + 8 * a.N;
     m.gs = 1; m.g = gl.data(); m.gg = m.g + 6 * a.N;
     for (int64_t i = 0; i < B; ++i) {
         if (a.M == 5) emul_one<5>(a, m, i);
