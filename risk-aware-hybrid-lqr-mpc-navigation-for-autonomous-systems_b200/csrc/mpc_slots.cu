@@ -728,6 +728,18 @@ k_mpc_slots(const MpcArgs a) {
             if (cnt) {
                 const int nth = __fns(vmask, 0, (lane < cnt ? lane : 0) + 1);
                 const int dk = 32 / cnt, dn = 32 - dk * cnt;
+                // the fresh lanes' own scalars and obstacle rows go first: their latency hides behind the row loop
+                double ox0x = 0.0, ox0y = 0.0, ox0t = 0.0, or0x = 0.0, or0y = 0.0, or0t = 0.0;
+                if (fresh) {
+                    const int64_t B = a.B;
+                    ox0x = __ldg(a.x0 + id); ox0y = __ldg(a.x0 + B + id); ox0t = __ldg(a.x0 + 2 * B + id);
+                    or0x = __ldg(a.xref + id); or0y = __ldg(a.xref + B + id); or0t = __ldg(a.xref + 2 * B + id);
+                    const int M3 = 3 * ((MT >= 0) ? MT : a.M);
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(&MO(0));
+                    for (int e = 0; e < M3; ++e)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;"
+                                     :: "r"(dst + (unsigned)(e * SS * 8)), "l"(a.obs + (int64_t)e * B + id) : "memory");
+                }
                 int k = lane / cnt, n = lane - k * cnt;
                 for (int t = lane; t - lane < T; t += 32) {
                     const int tl = __shfl_sync(FULL, nth, n);
@@ -741,22 +753,29 @@ k_mpc_slots(const MpcArgs a) {
                     if (n >= cnt) { n -= cnt; ++k; }
                 }
                 TRACE(tr_x4 += clock64() - tr_c2;)
-                if (fresh) setup_owner<SS, MT>(a, m, s, id);      // its loads overlap the rows in flight
+                if (fresh) {                                      // the scalars loaded before the row loop
+                    s.inst = id; s.it = 0; s.ls = 0; s.rej = 0; s.st = B2C_MAXITER; s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
+                    s.x0x = ox0x; s.x0t = ox0t; s.r0x = or0x; s.r0t = or0t;
+                    s.z0x = ox0x - or0x; s.z0y = ox0y - or0y; s.z0t = b2c_wrap(ox0t - or0t);       // :392-401, :421
+                    s.mode = SLOT_FWD_PLAIN;
+                }
                 TRACE(__syncwarp(); tr_x5 += clock64() - tr_c2;)
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 __syncwarp();
                 TRACE(tr_x1 += clock64() - tr_c2; tr_c2 = clock64();)
-                // np.unwrap: a warp-wide look for any heading step of pi or more; only then the sequential pass
+                // np.unwrap: each fresh lane looks along its own column for a heading step of pi or more (np.unwrap is
+                // the identity otherwise); only then the sequential pass.  The obstacle strip gets its d_safe + r.
                 bool jump = false;
-                k = lane / cnt; n = lane - k * cnt;
-                for (int t = lane; t - lane < T; t += 32) {
-                    const int tl = __shfl_sync(FULL, nth, n);
-                    if (t < T && k > 0) {
-                        const double* u = m.u + (tl - lane);
-                        jump |= !(fabs(u[(size_t)(8 * k) * SS] - u[(size_t)(8 * k - 8) * SS]) < 3.141592653589793);
+                if (fresh) {
+                    const int M3 = 3 * ((MT >= 0) ? MT : a.M);
+                    for (int e = 2; e < M3; e += 3) MO(e) = a.d_safe + MO(e);
+                    double prev = MU(0);
+#pragma unroll 4
+                    for (int kk = 1; kk < a.N; ++kk) {
+                        const double cur = MU(8 * kk);
+                        jump |= !(fabs(cur - prev) < 3.141592653589793);
+                        prev = cur;
                     }
-                    k += dk; n += dn;
-                    if (n >= cnt) { n -= cnt; ++k; }
                 }
                 const bool any_jump = __any_sync(FULL, jump);
                 if (fresh) setup_unwrap<SS>(a, m, s, any_jump);
