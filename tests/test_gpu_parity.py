@@ -484,3 +484,35 @@ def test_mpc_lti_hard_rows_scalar_api(hc):
             assert abs(sol.cost - o["cost"]) <= 1e-6 * abs(o["cost"])
             assert np.abs(sol.predicted_states - o["predicted_states"]).max() <= 1e-5
     assert verdicts == {"optimal", "fallback"}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,M,B", [(20, 5, 3000), (6, 3, 700), (20, 5, 40)])
+def test_mpc_slot_kernel_helper_lanes_follow_the_sequential_line_search(hc, N, M, B):
+    """Helper lanes (mpc_slots.cu: idle lanes of a warp evaluate the next trial steps of an instance whose trial was
+    rejected) must reproduce the SEQUENTIAL line search: same iteration count and status per instance as the host
+    emulation of the per-lane state machine (which has no helpers), results equal to rounding of the device's
+    sincos / reciprocal.  The batch sits deep inside the obstacles (large start offsets), so most instances see
+    rejected trials, and it is small enough for the whole launch to run in tail mode (helpers reserved from the
+    first round on)."""
+    import emul
+    from hybrid_controller.controllers.mpc_controller import MPCController
+    from hybrid_controller import workloads as wl, _native as nat
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=5 * N + M, obstacles=wl.DENSE_OBSTACLES[:M],
+                                          pos_jitter=0.35, th_jitter=0.6, obs_jitter=0.3)
+    mpc = MPCController(horizon=N, block_size=1, **wl.SIM_MPC)
+    mpc.engine = 2
+    out = mpc.solve_with_ltv_batch(x0, xr, ur, ob)
+    p = nat.mpc_params(nat.MPC_LTV, N, M, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02)
+    ref = emul.mpc(p, x0, xr, ur, ob, slots=True)
+    assert np.array_equal(out["status"], ref["status"]) and (out["status"] == 0).all()
+    same = out["iters"] == ref["iters"]
+    # an iteration count may differ only where the decrement sits at the stopping threshold (device vs host libm)
+    assert same.mean() >= 0.995 and np.abs(out["iters"] - ref["iters"]).max() <= 1
+    assert out["iters"].max() >= 5                               # the batch does contain long line searches
+    assert np.abs(out["u0"] - ref["u0"]).max() <= 1e-9
+    assert (np.abs(out["cost"] - ref["cost"]) <= 1e-10 * np.abs(ref["cost"])).all()
+    assert np.abs(out["useq"] - ref["useq"]).max() <= 1e-8 and np.abs(out["xpred"] - ref["xpred"]).max() <= 1e-8
+    again = mpc.solve_with_ltv_batch(x0, xr, ur, ob)             # helpers or not, a relaunch reproduces every bit
+    for key in ("u0", "cost", "iters", "useq", "xpred", "slack_used"):
+        assert np.array_equal(out[key], again[key]), key
