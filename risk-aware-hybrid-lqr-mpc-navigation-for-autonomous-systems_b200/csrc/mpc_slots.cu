@@ -587,22 +587,39 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
 // removes the tail a first-come queue leaves when the last instances claimed happen to be slow ones, and
 // keeps warps homogeneous (lanes of a warp finish, and refill, together).
 #define MPC_NCLASS 4
+// Stage loop outside, obstacles in registers (MT of them at a time): every reference position is read once, coalesced
+// across the warp, and the MT distance chains are independent -- 8 us for 65,536 instances instead of 34 with the
+// obstacle loop outside.
+template <int MT>
 B2C_HD int mpc_difficulty_class(const MpcArgs& a, int64_t i) {
     const int64_t B = a.B;
     int cls = MPC_NCLASS - 1;
-    for (int m = 0; m < a.M; ++m) {
-        const double ox = B2C_LDG(a.obs + (int64_t)(3 * m) * B + i), oy = B2C_LDG(a.obs + (int64_t)(3 * m + 1) * B + i);
-        const double c = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * m + 2) * B + i);
-        const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
-        const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
-        double d2min = 1e300;
-        for (int k = 0; k < a.N; ++k) {
-            const double dx = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i) - ox;
-            const double dy = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i) - oy;
-            d2min = fmin(d2min, dx * dx + dy * dy);
+    for (int m0 = 0; m0 < a.M; m0 += MT) {
+        double ox[MT], oy[MT], d2min[MT];
+#pragma unroll
+        for (int e = 0; e < MT; ++e) {
+            const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
+            ox[e] = B2C_LDG(a.obs + (int64_t)(3 * m) * B + i); oy[e] = B2C_LDG(a.obs + (int64_t)(3 * m + 1) * B + i);
+            d2min[e] = 1e300;
         }
-        const int cm_ = (d2min < t0) ? 0 : (d2min < t1) ? 1 : (d2min < t2) ? 2 : 3;
-        cls = (cm_ < cls) ? cm_ : cls;
+#pragma unroll 4
+        for (int k = 0; k < a.N; ++k) {
+            const double px = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i), py = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
+#pragma unroll
+            for (int e = 0; e < MT; ++e) {
+                const double dx = px - ox[e], dy = py - oy[e];
+                d2min[e] = fmin(d2min[e], dx * dx + dy * dy);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < MT; ++e) {
+            const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
+            const double c = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * m + 2) * B + i);
+            const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
+            const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
+            const int cm_ = (d2min[e] < t0) ? 0 : (d2min[e] < t1) ? 1 : (d2min[e] < t2) ? 2 : 3;
+            cls = (cm_ < cls) ? cm_ : cls;
+        }
     }
     return cls;
 }
@@ -614,7 +631,7 @@ __global__ void __launch_bounds__(128)
 k_mpc_classify(const MpcArgs a) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const int cls = (i < a.B) ? mpc_difficulty_class(a, i) : -1;
+    const int cls = (i < a.B) ? mpc_difficulty_class<5>(a, i) : -1;
 #pragma unroll
     for (int c = 0; c < MPC_NCLASS; ++c) {
         const unsigned mask = __ballot_sync(0xffffffffu, cls == c);
