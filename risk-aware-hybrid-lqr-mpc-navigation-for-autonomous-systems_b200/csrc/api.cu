@@ -8,7 +8,7 @@
 static thread_local std::string g_err;
 void b2c_set_error(const std::string& s) { g_err = s; }
 const char* b2c_last_error(void) { return g_err.c_str(); }
-int b2c_version(void) { return 110; }
+int b2c_version(void) { return 111; }
 
 int b2c_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     char buf[512];
