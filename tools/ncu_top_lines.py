@@ -1,5 +1,11 @@
+#!/usr/bin/env python3
+"""Stall samples per CUDA source line of one `ncu --set full --import-source on` capture.
+
+    ncu -i x.ncu-rep --page source --csv --print-source cuda,sass > /tmp/srcs.csv
+    python tools/ncu_top_lines.py [N] [/tmp/srcs.csv]
+Columns: share of all stall samples, share of executed warp instructions, file:line, source text, top stall reasons."""
 import csv, collections, sys
-rows=list(csv.reader(open('/tmp/srcs.csv')))
+rows=list(csv.reader(open(sys.argv[2] if len(sys.argv)>2 else '/tmp/srcs.csv')))
 col={}; fname=None
 lines=[]
 for r in rows:
