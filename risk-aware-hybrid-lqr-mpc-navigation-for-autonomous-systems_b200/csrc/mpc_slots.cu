@@ -626,23 +626,34 @@ B2C_HD int mpc_difficulty_class(const MpcArgs& a, int64_t i) {
 }
 
 #ifndef B2C_HOST_EMUL
-// perm[c*B + pos] = instance ids of class c in arrival order (warp-aggregated counters: a warp's 32
-// consecutive instances stay contiguous inside each class, so refills still read coalesced rows).
-__global__ void __launch_bounds__(128)
+// perm[c*B + pos] = instance ids of class c in arrival order.  Counters are aggregated per CTA of 512 instances (one
+// atomicAdd per class and CTA: 2,048 warps adding to the same four words serialised at L2 and were most of the
+// kernel's 21 us), so a CTA's instances stay contiguous and in index order inside each class.
+#define MPC_CLASSIFY_THREADS 512
+__global__ void __launch_bounds__(MPC_CLASSIFY_THREADS)
 k_mpc_classify(const MpcArgs a) {
+    __shared__ unsigned wcount[MPC_CLASSIFY_THREADS / 32][MPC_NCLASS];     // per warp, then exclusive prefix over warps
+    __shared__ unsigned long long cbase[MPC_NCLASS];
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cls = (i < a.B) ? mpc_difficulty_class<5>(a, i) : -1;
+    unsigned mymask = 0;
 #pragma unroll
     for (int c = 0; c < MPC_NCLASS; ++c) {
         const unsigned mask = __ballot_sync(0xffffffffu, cls == c);
-        if (!mask) continue;
-        const int leader = __ffs(mask) - 1;
-        unsigned long long base = 0;
-        if (lane == leader) base = atomicAdd(a.class_count + c, (unsigned long long)__popc(mask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (cls == c) a.perm[(int64_t)c * a.B + (int64_t)base + __popc(mask & ((1u << lane) - 1u))] = (uint32_t)i;
+        if (cls == c) mymask = mask;
+        if (lane == 0) wcount[warp][c] = __popc(mask);
     }
+    __syncthreads();
+    if (threadIdx.x < MPC_NCLASS) {
+        const int c = threadIdx.x;
+        unsigned tot = 0;
+        for (int w = 0; w < MPC_CLASSIFY_THREADS / 32; ++w) { const unsigned n = wcount[w][c]; wcount[w][c] = tot; tot += n; }
+        cbase[c] = tot ? atomicAdd(a.class_count + c, (unsigned long long)tot) : 0ull;
+    }
+    __syncthreads();
+    if (cls >= 0)
+        a.perm[(int64_t)cls * a.B + (int64_t)cbase[cls] + wcount[warp][cls] + __popc(mymask & ((1u << lane) - 1u))] = (uint32_t)i;
 }
 #endif
 
@@ -962,7 +973,7 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     B2C_CUDA(cudaMemsetAsync(a.queue, 0, (1 + MPC_NCLASS) * sizeof(unsigned long long), ctx->stream));
     if (ordered) {
         a.perm = (uint32_t*)((char*)ctx->scratch + strip + 256);
-        k_mpc_classify<<<b2c_blocks(a.B, 128), 128, 0, ctx->stream>>>(a);
+        k_mpc_classify<<<b2c_blocks(a.B, MPC_CLASSIFY_THREADS), MPC_CLASSIFY_THREADS, 0, ctx->stream>>>(a);
         B2C_CHECK_LAUNCH(ctx);
     }
     // obstacle rows unrolled at compile time for the two shapes the reference runs (M = 3, 5)
