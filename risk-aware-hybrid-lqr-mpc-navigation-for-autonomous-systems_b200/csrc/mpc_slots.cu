@@ -591,69 +591,90 @@ B2C_HD void slot_phase_forward(const MpcArgs& a, const SlotMem& m, SlotState& s)
 // across the warp, and the MT distance chains are independent -- 21 us for 65,536 instances instead of 34 with the
 // obstacle loop outside.  (Four lanes per instance with a shuffle-min: 31 us, and the claim order then groups only 8
 // consecutive instances per warp, which costs the refill its coalescing -- measured 0.473 ms per batch against 0.450.)
+#ifndef B2C_HOST_EMUL
+// min over stages [k0, k1) of the squared distance from the reference position to obstacle m0 + e, e < MT
 template <int MT>
-B2C_HD int mpc_difficulty_class(const MpcArgs& a, int64_t i) {
+__device__ __forceinline__ void mpc_ref_d2min(const MpcArgs& a, int64_t i, int m0, int k0, int k1, double (&d2min)[MT]) {
     const int64_t B = a.B;
-    int cls = MPC_NCLASS - 1;
-    for (int m0 = 0; m0 < a.M; m0 += MT) {
-        double ox[MT], oy[MT], d2min[MT];
+    double ox[MT], oy[MT];
+#pragma unroll
+    for (int e = 0; e < MT; ++e) {
+        const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
+        ox[e] = __ldg(a.obs + (int64_t)(3 * m) * B + i); oy[e] = __ldg(a.obs + (int64_t)(3 * m + 1) * B + i);
+        d2min[e] = 1e300;
+    }
+#pragma unroll 5
+    for (int k = k0; k < k1; ++k) {
+        const double px = __ldg(a.xref + (int64_t)(3 * k) * B + i), py = __ldg(a.xref + (int64_t)(3 * k + 1) * B + i);
 #pragma unroll
         for (int e = 0; e < MT; ++e) {
-            const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
-            ox[e] = B2C_LDG(a.obs + (int64_t)(3 * m) * B + i); oy[e] = B2C_LDG(a.obs + (int64_t)(3 * m + 1) * B + i);
-            d2min[e] = 1e300;
-        }
-#pragma unroll 4
-        for (int k = 0; k < a.N; ++k) {
-            const double px = B2C_LDG(a.xref + (int64_t)(3 * k) * B + i), py = B2C_LDG(a.xref + (int64_t)(3 * k + 1) * B + i);
-#pragma unroll
-            for (int e = 0; e < MT; ++e) {
-                const double dx = px - ox[e], dy = py - oy[e];
-                d2min[e] = fmin(d2min[e], dx * dx + dy * dy);
-            }
-        }
-#pragma unroll
-        for (int e = 0; e < MT; ++e) {
-            const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
-            const double c = a.d_safe + B2C_LDG(a.obs + (int64_t)(3 * m + 2) * B + i);
-            const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
-            const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
-            const int cm_ = (d2min[e] < t0) ? 0 : (d2min[e] < t1) ? 1 : (d2min[e] < t2) ? 2 : 3;
-            cls = (cm_ < cls) ? cm_ : cls;
+            const double dx = px - ox[e], dy = py - oy[e];
+            d2min[e] = fmin(d2min[e], dx * dx + dy * dy);
         }
     }
-    return cls;
 }
+#endif
 
 #ifndef B2C_HOST_EMUL
-// perm[c*B + pos] = instance ids of class c in arrival order.  Counters are aggregated per CTA of 512 instances (one
+// perm[c*B + pos] = instance ids of class c in arrival order.  Counters are aggregated per CTA of 256 instances (one
 // atomicAdd per class and CTA: 2,048 warps adding to the same four words serialised at L2 and were most of the
 // kernel's 21 us), so a CTA's instances stay contiguous and in index order inside each class.
 #define MPC_CLASSIFY_THREADS 512
+#define MPC_CLASSIFY_INST 256                         // instances per CTA: two threads each (first / second half of the horizon)
 __global__ void __launch_bounds__(MPC_CLASSIFY_THREADS)
 k_mpc_classify(const MpcArgs a) {
-    __shared__ unsigned wcount[MPC_CLASSIFY_THREADS / 32][MPC_NCLASS];     // per warp, then exclusive prefix over warps
+    constexpr int MT = 5;
+    __shared__ double half2[MT][MPC_CLASSIFY_INST];                        // second half's minima
+    __shared__ unsigned wcount[MPC_CLASSIFY_INST / 32][MPC_NCLASS];        // per warp, then exclusive prefix over warps
     __shared__ unsigned long long cbase[MPC_NCLASS];
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cls = (i < a.B) ? mpc_difficulty_class<5>(a, i) : -1;
+    const int li = threadIdx.x & (MPC_CLASSIFY_INST - 1), half = threadIdx.x / MPC_CLASSIFY_INST;
+    const int64_t i = (int64_t)blockIdx.x * MPC_CLASSIFY_INST + li, B = a.B;
+    const bool valid = i < B;
+    const int lane = threadIdx.x & 31, warp = li >> 5;
+    const int kh = a.N / 2;
+    int cls = MPC_NCLASS - 1;
+    for (int m0 = 0; m0 < a.M; m0 += MT) {             // uniform trip count: barriers inside
+        double d2min[MT];
+#pragma unroll
+        for (int e = 0; e < MT; ++e) d2min[e] = 1e300;
+        if (valid) mpc_ref_d2min<MT>(a, i, m0, half ? kh : 0, half ? a.N : kh, d2min);
+        if (half) {
+#pragma unroll
+            for (int e = 0; e < MT; ++e) half2[e][li] = d2min[e];
+        }
+        __syncthreads();
+        if (!half && valid) {
+#pragma unroll
+            for (int e = 0; e < MT; ++e) {
+                const double d2 = fmin(d2min[e], half2[e][li]);
+                const int m = (m0 + e < a.M) ? (m0 + e) : (a.M - 1);
+                const double c = a.d_safe + __ldg(a.obs + (int64_t)(3 * m + 2) * B + i);
+                const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
+                const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
+                const int cm_ = (d2 < t0) ? 0 : (d2 < t1) ? 1 : (d2 < t2) ? 2 : 3;
+                cls = (cm_ < cls) ? cm_ : cls;
+            }
+        }
+        __syncthreads();
+    }
+    if (half || !valid) cls = -1;
     unsigned mymask = 0;
 #pragma unroll
     for (int c = 0; c < MPC_NCLASS; ++c) {
         const unsigned mask = __ballot_sync(0xffffffffu, cls == c);
         if (cls == c) mymask = mask;
-        if (lane == 0) wcount[warp][c] = __popc(mask);
+        if (lane == 0 && !half) wcount[warp][c] = __popc(mask);
     }
     __syncthreads();
     if (threadIdx.x < MPC_NCLASS) {
         const int c = threadIdx.x;
         unsigned tot = 0;
-        for (int w = 0; w < MPC_CLASSIFY_THREADS / 32; ++w) { const unsigned n = wcount[w][c]; wcount[w][c] = tot; tot += n; }
+        for (int w = 0; w < MPC_CLASSIFY_INST / 32; ++w) { const unsigned n = wcount[w][c]; wcount[w][c] = tot; tot += n; }
         cbase[c] = tot ? atomicAdd(a.class_count + c, (unsigned long long)tot) : 0ull;
     }
     __syncthreads();
     if (cls >= 0)
-        a.perm[(int64_t)cls * a.B + (int64_t)cbase[cls] + wcount[warp][cls] + __popc(mymask & ((1u << lane) - 1u))] = (uint32_t)i;
+        a.perm[(int64_t)cls * B + (int64_t)cbase[cls] + wcount[warp][cls] + __popc(mymask & ((1u << lane) - 1u))] = (uint32_t)i;
 }
 #endif
 
@@ -973,7 +994,7 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int tpb) {
     B2C_CUDA(cudaMemsetAsync(a.queue, 0, (1 + MPC_NCLASS) * sizeof(unsigned long long), ctx->stream));
     if (ordered) {
         a.perm = (uint32_t*)((char*)ctx->scratch + strip + 256);
-        k_mpc_classify<<<b2c_blocks(a.B, MPC_CLASSIFY_THREADS), MPC_CLASSIFY_THREADS, 0, ctx->stream>>>(a);
+        k_mpc_classify<<<b2c_blocks(a.B, MPC_CLASSIFY_INST), MPC_CLASSIFY_THREADS, 0, ctx->stream>>>(a);
         B2C_CHECK_LAUNCH(ctx);
     }
     // obstacle rows unrolled at compile time for the two shapes the reference runs (M = 3, 5)
