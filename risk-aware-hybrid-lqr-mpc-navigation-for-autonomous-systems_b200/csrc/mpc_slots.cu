@@ -691,17 +691,25 @@ __device__ __forceinline__ unsigned long long trace_ns() {
 #endif
 // Helper lanes (the tail of a batch).  The kernel's makespan at BASELINE's batch size is the latency of its
 // hardest instances: 13 Newton iterations plus as many rejected trial steps, one forward sweep each.  An instance
-// that has had a trial rejected (s.rej) therefore keeps up to MPC_SPEC_HELPERS idle lanes of its warp from
+// that has had a trial rejected (s.rej) therefore keeps MPC_SPEC_HELPERS (or all, see MPC_SPEC_FEW) idle lanes of its warp from
 // refilling while the queue is short (remaining <= MPC_SPEC_TAIL x resident slots), and those lanes evaluate the
 // NEXT trial steps of the same iteration (alpha/2, alpha/4, ...) in the same round, on copies of the owner's strips.
 // The first trial of the sequence that decreases the cost is taken -- the sequence and every sweep are those of
 // the sequential line search, so results do not depend on whether, or how many, helpers were there.  If the winner
 // is a helper, the instance simply continues on that lane (state by shuffle, the two lanes swap global strips).
 #ifndef MPC_SPEC_HELPERS
-#define MPC_SPEC_HELPERS 3
+#define MPC_SPEC_HELPERS 8
 #endif
 #ifndef MPC_SPEC_TAIL
 #define MPC_SPEC_TAIL 4
+#endif
+// a warp with at most MPC_SPEC_FEW such instances keeps ALL its idle lanes back (it stops refilling: its rounds lose the
+// refill phase and every trial step of an iteration is evaluated at once); with more of them, MPC_SPEC_HELPERS lanes each.
+// Measured on config 4 (ms per 65,536 batch): 3 helpers flat 0.441, 8 flat 0.426, 31 flat 0.405 -- but a flat 31 makes the
+// closed-loop rollouts (N = 6, many instances with rejected trials per warp) bimodal, 0.32 s or 0.95 s per config-5 shard,
+// because whole warps stall behind their requesters; FEW = 2 with 8 helpers: 0.410 and the shard stays at 0.315 s.
+#ifndef MPC_SPEC_FEW
+#define MPC_SPEC_FEW 2
 #endif
 template <int SS, int MT>
 __global__ void __launch_bounds__(SS, 1)
@@ -745,7 +753,10 @@ k_mpc_slots(const MpcArgs a) {
         const unsigned idle0 = __ballot_sync(FULL, s.mode == SLOT_IDLE);
         const unsigned req_m = __ballot_sync(FULL, s.mode == SLOT_FWD_GAIN && s.rej);
         int keep = 0;
-        if (req_m && (a.B - seen) <= (int64_t)MPC_SPEC_TAIL * a.nslots) keep = MPC_SPEC_HELPERS * __popc(req_m);
+        if (req_m && (a.B - seen) <= (int64_t)MPC_SPEC_TAIL * a.nslots) {
+            const int nreq = __popc(req_m);
+            keep = ((nreq <= MPC_SPEC_FEW) ? 31 : MPC_SPEC_HELPERS) * nreq;
+        }
         const bool want = (s.mode == SLOT_IDLE) && !empty && (__popc(idle0 & lt_mask) < __popc(idle0) - keep);
         const unsigned need = __ballot_sync(FULL, want);
         if (need) {
