@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import emul
-from conftest import DEFAULT_OBS, MPC_PRM6
+from conftest import DEFAULT_OBS, MPC_PRM6, assert_g_mpc_closed_loop
 from oracle import lin_dare, rollout as oro
 
 pytestmark = pytest.mark.gpu
@@ -36,8 +36,7 @@ def test_rollout_mpc_mode_vs_g_mpc(golden):
     _, mpc, _ = _controllers(N=6, block_size=2)
     table = lin_dare.figure8(20.0)
     out = simulate_batch("mpc", table, [0], table[0:1, 1:4], np.array(DEFAULT_OBS), 998, mpc=mpc, mpc_rate=5, log=True)
-    assert np.abs(out["states"][0] - g["states"][:999]).max() < 5e-4           # the log's own OSQP eps re-enters the loop
-    assert np.abs(out["controls"][0] - g["controls"][:998]).max() < 5e-3
+    assert_g_mpc_closed_loop(out["states"][0], out["controls"][0], g["states"][:999], g["controls"][:998])
     assert out["mpc_solves"][0] == 200 and out["mpc_fallbacks"][0] == 0
     # collision census of run_mpc_simulation (:288-293): states inside radius + d_safe of any obstacle
     ob = np.array(DEFAULT_OBS)

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 import emul
-from conftest import MPC_PRM6, MPC_PRM20, DEFAULT_OBS, ROOT
+from conftest import MPC_PRM6, MPC_PRM20, DEFAULT_OBS, ROOT, g_mpc_open_loop_tol, assert_g_mpc_closed_loop
 from oracle import lin_dare, mpc_qp
 
 
@@ -140,7 +140,7 @@ def test_emul_mpc_g_mpc_golden(golden):
     slack_ticks = set(g["slack_ticks"].tolist())
     err = np.abs(out["u0"] - g["controls"][ks]).max(axis=1)
     for k, e in zip(ks, err):
-        assert e < (2e-3 if k in slack_ticks else 5e-6), (k, e)
+        assert e <= g_mpc_open_loop_tol(int(k), slack_ticks), (k, e)
     assert sorted(ks[out["slack_used"] == 1].tolist()) == sorted(slack_ticks)
 
 
@@ -176,15 +176,16 @@ def test_emul_mpc_infeasible_blocked_bounds():
 
 def test_emul_mpc_closed_loop_vs_g_mpc(golden):
     """Config 2 closed loop (run_mpc_simulation: solve every 5th tick, hold u, Euler plant) vs the
-    shipped log.  Stated tolerance: states 5e-4, controls 5e-3 -- the log's own OSQP eps=1e-5 error
-    (1.4e-3 on a slack-active control) re-enters the loop through the plant; slack ticks identical."""
+    shipped log.  Bands of conftest.assert_g_mpc_closed_loop: 1e-9 up to tick 29, then states 5e-4 / controls 5e-3
+    (the logged k=30 solve is an unpolished OSQP iterate, 1.37e-3 off, and re-enters the log's own loop); slack
+    ticks identical."""
     g = golden["g_mpc"]
     traj = lin_dare.figure8(20.0)
     obs = np.array(DEFAULT_OBS)
     prm = _params(6, 3, 2)
     x = traj[0, 1:4].copy()
     sc = np.zeros(1, np.int32)
-    ex = eu = 0.0
+    xs, us = [], []
     slack = []
     for k in range(999):
         if k % 5 == 0:
@@ -193,10 +194,9 @@ def test_emul_mpc_closed_loop_vs_g_mpc(golden):
             sc, u = o["step_count"], o["u0"][0]
             if o["slack_used"][0]:
                 slack.append(k)
-        ex = max(ex, np.abs(x - g["states"][k]).max())
-        eu = max(eu, np.abs(u - g["controls"][k]).max())
+        xs.append(x.copy()); us.append(u.copy())
         x = lin_dare.plant_step(x, u, .02, 2., 3.)
-    assert ex < 5e-4 and eu < 5e-3, (ex, eu)
+    assert_g_mpc_closed_loop(xs, us, g["states"], g["controls"])
     assert slack == g["slack_ticks"].tolist()
 
 

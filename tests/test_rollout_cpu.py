@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import emul
-from conftest import DEFAULT_OBS, GOLDEN, MPC_PRM6
+from conftest import DEFAULT_OBS, GOLDEN, MPC_PRM6, assert_g_mpc_closed_loop
 from oracle import lin_dare, rollout as oro
 
 
@@ -73,8 +73,7 @@ def test_emul_rollout_mpc_mode_vs_g_mpc(golden):
     _, mpc, _ = _controllers(N=6, block_size=2)
     table = lin_dare.figure8(20.0)
     out = emul.rollout("mpc", table, [0], table[0:1, 1:4], np.array(DEFAULT_OBS), 998, mpc=mpc, mpc_rate=5)
-    assert np.abs(out["states"][0] - g["states"][:999]).max() < 5e-4
-    assert np.abs(out["controls"][0] - g["controls"][:998]).max() < 5e-3
+    assert_g_mpc_closed_loop(out["states"][0], out["controls"][0], g["states"][:999], g["controls"][:998])
     assert out["mpc_solves"][0] == 200 and out["mpc_fallbacks"][0] == 0
 
 
