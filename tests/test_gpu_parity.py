@@ -197,6 +197,15 @@ def _violations(mpc, x0, xr, ur, ob, out, b, bs=1):
     return max(box, 0.0), J
 
 
+def _one_blas_thread():
+    # the pool already uses every core: without this each worker's BLAS spawns a thread per core (800 s instead of 5)
+    try:
+        from threadpoolctl import threadpool_limits
+        _one_blas_thread.limit = threadpool_limits(1)
+    except Exception:
+        pass
+
+
 def _oracle_config4(args):
     from oracle import mpc_qp
     x0, xr, ur, ob = args
@@ -214,7 +223,7 @@ def config4_oracle():
     B = 1024
     x0, xr, ur, ob = wl.config4_instances(B, N=20, seed=0)
     cores = len(os.sched_getaffinity(0))
-    with mp.get_context("fork").Pool(cores) as pool:
+    with mp.get_context("fork").Pool(cores, initializer=_one_blas_thread) as pool:
         res = pool.map(_oracle_config4, [(x0[b], xr[b], ur[b], ob[b]) for b in range(B)], chunksize=8)
     return (x0, xr, ur, ob), res
 
