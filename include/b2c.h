@@ -26,7 +26,8 @@
  *     (stream, scratch, pinned staging);
  *   - return value: 0 = ok, <0 = error (b2c_last_error() gives the text). Per-instance solver
  *     outcomes are reported in status[] and never as an error code;
- *   - a context is not thread-safe: one per host thread / per GPU.
+ *   - a context is not thread-safe: one per host thread / per GPU.  Every entry point runs on the context's device
+ *     whatever the caller's current device is, and leaves the caller's current device unchanged;
  *   - there is NO CPU fallback: without a CUDA device b2c_create fails.
  */
 #ifndef B2C_H
@@ -67,7 +68,8 @@ typedef struct {
     int32_t soft;             /* use_soft_constraints (:152, :347).  0 = hard obstacle rows (:197-200, :260-270,
                                  :383-386, :464-468): solved by the method of multipliers in the general kernel;
                                  rows that cannot be met give status B2C_INFEASIBLE and the fallback outputs   */
-    int32_t max_iter;         /* Newton iteration cap (<=0: default 60)                         */
+    int32_t max_iter;         /* Newton iteration cap (<=0: default 60; 2000 with hard rows, where it
+                                 covers all multiplier rounds together)                          */
     int32_t ramp_up_steps;    /* cold-start ramp length       (:144), LTV only                  */
     int32_t engine;           /* kernel choice: 0 = automatic, 1 = general kernel (HBM scratch), 2 = persistent
                                  slot kernel (shared-memory scratch; LTV, block_size 1, soft rows) or error -5 */
@@ -82,6 +84,7 @@ int         b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream);
 void        b2c_destroy(b2c_ctx* ctx);
 const char* b2c_last_error(void);
 int         b2c_version(void);
+int         b2c_current_device(int* out);                     /* the calling thread's current CUDA device */
 int         b2c_sync(b2c_ctx* ctx);                           /* cudaStreamSynchronize          */
 void*       b2c_stream(b2c_ctx* ctx);                         /* the cudaStream_t in use        */
 /* total kernel launches issued through this context since creation */
@@ -121,6 +124,11 @@ int b2c_dare_host(b2c_ctx*, int64_t B, int method, int guard, double dt,
 int b2c_lqr_control_dev(b2c_ctx*, int64_t B, double v_max, double w_max,
                         const double* x, const double* xref, const double* uref,
                         const double* K, double* u, double* err);
+
+/* host: numpy layouts x, xref (B,3); uref (B,2); K (B,2,3) -> u (B,2), err (B,3) or NULL                       */
+int b2c_lqr_control_host(b2c_ctx*, int64_t B, double v_max, double w_max,
+                         const double* x, const double* xref, const double* uref,
+                         const double* K, double* u, double* err);
 
 /* ---- K3: MPC QP ---------------------------------------------------------------------------- */
 /* bytes of device scratch b2c_mpc_dev needs for (B, params); the context grows its own scratch

@@ -8,7 +8,13 @@
 static thread_local std::string g_err;
 void b2c_set_error(const std::string& s) { g_err = s; }
 const char* b2c_last_error(void) { return g_err.c_str(); }
-int b2c_version(void) { return 111; }
+int b2c_version(void) { return 200; }
+int b2c_current_device(int* out) {
+    if (!out) { b2c_set_error("null out pointer"); return -1; }
+    cudaError_t e = cudaGetDevice(out);
+    if (e != cudaSuccess) { *out = -1; b2c_set_error(std::string("no CUDA device: ") + cudaGetErrorString(e)); return -10; }
+    return 0;
+}
 
 int b2c_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     char buf[512];
@@ -42,12 +48,13 @@ int b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream) {
         return -10;
     }
     if (device < 0) B2C_CUDA(cudaGetDevice(&device));
-    B2C_CUDA(cudaSetDevice(device));
+    if (device >= ndev) { b2c_set_error("no such CUDA device"); return -11; }
     b2c_ctx* c = new b2c_ctx();
-    c->device = device;
-    cudaDeviceProp prop;
-    B2C_CUDA(cudaGetDeviceProperties(&prop, device));
-    c->sm_count = prop.multiProcessorCount;
+    c->device = device;                               // the caller's current device is left as it is
+    int sms = 0;
+    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) { delete c; return b2c_cuda_fail(e, "device attribute", __FILE__, __LINE__); }
+    c->sm_count = sms;
     // the caller's stream is used as given -- a null handle is the legacy default stream
     c->stream = (cudaStream_t)cuda_stream; c->own_stream = false;
     *out = c;
@@ -57,7 +64,9 @@ int b2c_create_on_stream(b2c_ctx** out, int device, void* cuda_stream) {
 int b2c_create(b2c_ctx** out, int device) {
     int rc = b2c_create_on_stream(out, device, nullptr);
     if (rc) return rc;
-    cudaError_t e = cudaStreamCreateWithFlags(&(*out)->stream, cudaStreamNonBlocking);
+    B2cDeviceGuard guard((*out)->device);
+    cudaError_t e = guard.err;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&(*out)->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete *out; *out = nullptr; return b2c_cuda_fail(e, "stream create", __FILE__, __LINE__); }
     (*out)->own_stream = true;
     return 0;
@@ -65,23 +74,30 @@ int b2c_create(b2c_ctx** out, int device) {
 
 void b2c_destroy(b2c_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->device);
+    B2cDeviceGuard guard(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->scratch) cudaFree(c->scratch);
     if (c->dstage) cudaFree(c->dstage);
     if (c->hstage) cudaFreeHost(c->hstage);
     for (int k = 0; k < 2; ++k) {
         if (c->lane_scratch[k]) cudaFree(c->lane_scratch[k]);
-        if (c->lane_stream[k]) cudaStreamDestroy(c->lane_stream[k]);
+        if (c->lane_stream[k]) { cudaStreamSynchronize(c->lane_stream[k]); cudaStreamDestroy(c->lane_stream[k]); }
     }
-    if (c->out_stream) cudaStreamDestroy(c->out_stream);
+    if (c->out_stream) { cudaStreamSynchronize(c->out_stream); cudaStreamDestroy(c->out_stream); }
     for (int k = 0; k < 16; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
+    for (int k = 0; k < 2; ++k) {
+        if (c->job[k].d) cudaFree(c->job[k].d);
+        if (c->job[k].done) cudaEventDestroy(c->job[k].done);
+    }
+    if (c->aux) cudaFree(c->aux);
+    if (c->aux2) cudaFree(c->aux2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 
 int b2c_sync(b2c_ctx* c) {
     if (!c) { b2c_set_error("null context"); return -1; }
+    B2C_DEVICE_GUARD(c);
     B2C_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -176,7 +192,7 @@ int b2c_linearize_host(b2c_ctx* c, int64_t B, int method, int guard, double dt,
     if (!c) { b2c_set_error("null context"); return -1; }
     if (method < 0 || method > 2) { b2c_set_error("Unknown discretization method"); return -2; }
     if (B <= 0) return 0;
-    B2C_CUDA(cudaSetDevice(c->device));
+    B2C_DEVICE_GUARD(c);
     size_t need = 2 * pad256(B * 8) + pad256(B * 72) + pad256(B * 48);
     int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
     if (rc) return rc;
@@ -198,7 +214,7 @@ int b2c_dare_host(b2c_ctx* c, int64_t B, int method, int guard, double dt,
                   double* K, double* P, int32_t* iters, int32_t* status) {
     if (!c) { b2c_set_error("null context"); return -1; }
     if (B <= 0) return 0;
-    B2C_CUDA(cudaSetDevice(c->device));
+    B2C_DEVICE_GUARD(c);
     size_t need = 2 * pad256(B * 8) + 2 * pad256(B * 48) + pad256(B * 48) + pad256(B * 72) + 2 * pad256(B * 4);
     int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
     if (rc) return rc;
@@ -258,7 +274,7 @@ int b2c_mpc_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
     if (!c || !p) { b2c_set_error("null context/params"); return -1; }
     if (B <= 0) return 0;
     if (p->N < 1 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
-    B2C_CUDA(cudaSetDevice(c->device));
+    B2C_DEVICE_GUARD(c);
     const int N = p->N, M = p->M;
     const int FX = 3 * (N + 1), FU = 2 * N, FO = 3 * M;
     const size_t nin = (size_t)B * (3 + FX + FU + FO);
@@ -357,7 +373,7 @@ k_fma_peak(T* out, int iters, T a, T b) {
 
 int b2c_measure_fma_peak(b2c_ctx* c, int bits, double* tflops) {
     if (!c || !tflops) { b2c_set_error("null argument"); return -1; }
-    B2C_CUDA(cudaSetDevice(c->device));
+    B2C_DEVICE_GUARD(c);
     int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, 4096, false);
     if (rc) return rc;
     const int iters = 4096, blocks = c->sm_count * 8, threads = 256;

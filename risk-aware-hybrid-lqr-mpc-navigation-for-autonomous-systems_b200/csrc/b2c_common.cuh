@@ -28,7 +28,31 @@ struct b2c_ctx {
     void* lane_scratch[2] = {nullptr, nullptr};
     size_t lane_scratch_bytes[2] = {0, 0};
     cudaEvent_t ev[16] = {};
+    int64_t chunk_seq = 0;                 // chunks issued so far (alternates the compute lanes across calls too)
+    // third device arena (materialised table segments for the general kernel)
+    void* aux = nullptr;
+    size_t aux_bytes = 0;
+    void* aux2 = nullptr;                  // device copies of b2c_rollout_host's arguments
+    size_t aux2_bytes = 0;
+    // the *_host MPC entry points double-buffer their device staging so that an asynchronous call can copy its
+    // inputs while the previous call is still solving: at most two calls in flight
+    struct HostJob { void* d = nullptr; size_t bytes = 0; cudaEvent_t done = nullptr; bool pending = false; } job[2];
+    int job_next = 0;
 };
+
+// Every entry point runs on the context's device whatever the caller's current device is, and leaves the
+// caller's current device as it found it (one process may drive several GPUs with one context each).
+struct B2cDeviceGuard {
+    int prev = -1; cudaError_t err = cudaSuccess;
+    explicit B2cDeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) err = cudaSetDevice(dev); else prev = -1;
+    }
+    ~B2cDeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define B2C_DEVICE_GUARD(ctx)                                                   \
+    B2cDeviceGuard _b2c_dg((ctx)->device);                                      \
+    if (_b2c_dg.err != cudaSuccess) return b2c_cuda_fail(_b2c_dg.err, "cudaSetDevice", __FILE__, __LINE__)
 
 void b2c_set_error(const std::string& s);
 int b2c_cuda_fail(cudaError_t e, const char* what, const char* file, int line);

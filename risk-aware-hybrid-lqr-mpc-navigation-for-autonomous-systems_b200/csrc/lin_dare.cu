@@ -84,6 +84,7 @@ int b2c_linearize_dev(b2c_ctx* ctx, int64_t B, int method, int guard, double dt,
     if (!ctx) { b2c_set_error("null context"); return -1; }
     if (method < 0 || method > 2) { b2c_set_error("Unknown discretization method"); return -2; }
     if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
     k_linearize_soa<<<b2c_blocks(B, 256), 256, 0, ctx->stream>>>(B, method, guard, dt, v, th, Ad, Bd);
     B2C_CHECK_LAUNCH(ctx);
     return 0;
@@ -94,6 +95,7 @@ int b2c_linearize_packed_dev(b2c_ctx* ctx, int64_t B, int method, int guard, dou
     if (!ctx) { b2c_set_error("null context"); return -1; }
     if (method < 0 || method > 2) { b2c_set_error("Unknown discretization method"); return -2; }
     if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
     k_linearize_packed<<<b2c_blocks(B, LIN_TPB), LIN_TPB, 0, ctx->stream>>>(B, method, guard, dt, v, th, Ad, Bd);
     B2C_CHECK_LAUNCH(ctx);
     return 0;
@@ -274,6 +276,7 @@ int b2c_dare_dev(b2c_ctx* ctx, int64_t B, int method, int guard, double dt,
         b2c_set_error("DARE needs a discrete model (EULER or EXACT)"); return -2; }
     if (!(Rd[0] > 0.0) || !(Rd[1] > 0.0)) { b2c_set_error("R must be positive definite"); return -3; }
     if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
     k_dare<<<b2c_blocks(B, 128), 128, 0, ctx->stream>>>(B, method, guard, dt, Qd[0], Qd[1], Qd[2],
                                                          Rd[0], Rd[1], v, th, K, P, iters, status);
     B2C_CHECK_LAUNCH(ctx);
@@ -304,8 +307,57 @@ int b2c_lqr_control_dev(b2c_ctx* ctx, int64_t B, double v_max, double w_max,
                         const double* K, double* u, double* err) {
     if (!ctx) { b2c_set_error("null context"); return -1; }
     if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
     k_lqr_control<<<b2c_blocks(B, 256), 256, 0, ctx->stream>>>(B, v_max, w_max, x, xref, uref, K, u, err);
     B2C_CHECK_LAUNCH(ctx);
+    return 0;
+}
+
+// the same law on numpy-layout buffers: x, xref, err (B,3); uref, u (B,2); K (B,2,3)
+__global__ void __launch_bounds__(256)
+k_lqr_control_aos(int64_t B, double v_max, double w_max,
+                  const double* __restrict__ x, const double* __restrict__ xref,
+                  const double* __restrict__ uref, const double* __restrict__ K,
+                  double* __restrict__ u, double* __restrict__ err) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B) return;
+    const double* k = K + i * 6;
+    double e0 = x[3 * i] - xref[3 * i], e1 = x[3 * i + 1] - xref[3 * i + 1];
+    double e2 = b2c_wrap(x[3 * i + 2] - xref[3 * i + 2]);
+    double f0 = -k[0] * e0 + -k[1] * e1 + -k[2] * e2;
+    double f1 = -k[3] * e0 + -k[4] * e1 + -k[5] * e2;
+    u[2 * i] = b2c_clip(uref[2 * i] + f0, -v_max, v_max);
+    u[2 * i + 1] = b2c_clip(uref[2 * i + 1] + f1, -w_max, w_max);
+    if (err) { err[3 * i] = e0; err[3 * i + 1] = e1; err[3 * i + 2] = e2; }
+}
+
+int b2c_lqr_control_host(b2c_ctx* ctx, int64_t B, double v_max, double w_max,
+                         const double* x, const double* xref, const double* uref,
+                         const double* K, double* u, double* err) {
+    if (!ctx || !x || !xref || !uref || !K || !u) { b2c_set_error("null argument"); return -1; }
+    if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
+    const size_t b3 = (size_t)B * 24, b2 = (size_t)B * 16, b6 = (size_t)B * 48;
+    auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+    int rc = b2c_reserve(&ctx->dstage, &ctx->dstage_bytes, 3 * al(b3) + 2 * al(b2) + al(b6), false);
+    if (rc) return rc;
+    char* d = (char*)ctx->dstage;
+    double* dx = (double*)d; d += al(b3);
+    double* dxr = (double*)d; d += al(b3);
+    double* de = (double*)d; d += al(b3);
+    double* dur = (double*)d; d += al(b2);
+    double* du = (double*)d; d += al(b2);
+    double* dK = (double*)d;
+    cudaStream_t s = ctx->stream;
+    B2C_CUDA(cudaMemcpyAsync(dx, x, b3, cudaMemcpyHostToDevice, s));
+    B2C_CUDA(cudaMemcpyAsync(dxr, xref, b3, cudaMemcpyHostToDevice, s));
+    B2C_CUDA(cudaMemcpyAsync(dur, uref, b2, cudaMemcpyHostToDevice, s));
+    B2C_CUDA(cudaMemcpyAsync(dK, K, b6, cudaMemcpyHostToDevice, s));
+    k_lqr_control_aos<<<b2c_blocks(B, 256), 256, 0, s>>>(B, v_max, w_max, dx, dxr, dur, dK, du, err ? de : nullptr);
+    B2C_CHECK_LAUNCH(ctx);
+    B2C_CUDA(cudaMemcpyAsync(u, du, b2, cudaMemcpyDeviceToHost, s));
+    if (err) B2C_CUDA(cudaMemcpyAsync(err, de, b3, cudaMemcpyDeviceToHost, s));
+    B2C_CUDA(cudaStreamSynchronize(s));
     return 0;
 }
 

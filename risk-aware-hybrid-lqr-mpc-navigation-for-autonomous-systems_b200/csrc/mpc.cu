@@ -578,6 +578,7 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
     if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
     if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
     MpcArgs a;
     mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
     int tpb = 0;

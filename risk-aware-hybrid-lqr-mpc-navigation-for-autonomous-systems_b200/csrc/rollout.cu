@@ -235,7 +235,7 @@ int b2c_rollout_dev(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const 
     int rc = roll_fill(g, R, p);
     if (rc) return rc;
     if (g.M > 0 && !obs) { b2c_set_error("obstacles missing"); return -1; }
-    B2C_CUDA(cudaSetDevice(ctx->device));
+    B2C_DEVICE_GUARD(ctx);
     const bool qp = p->mode != B2C_ROLL_LQR;
     const int N = g.N, M = g.M, rows = g.rows;
     // ---- working memory (context-owned, second arena so that the K3 scratch stays untouched) ---------------
@@ -316,7 +316,7 @@ int b2c_rollout_host(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const
                      double* log_x, double* log_u, double* log_risk, int8_t* log_ctrl) {
     if (!ctx || !p || !table || !k0 || !x || !counters || !stats) { b2c_set_error("null argument"); return -1; }
     if (R <= 0) return 0;
-    B2C_CUDA(cudaSetDevice(ctx->device));
+    B2C_DEVICE_GUARD(ctx);
     const int M = p->mpc.M, T = p->ticks;
     const size_t b_tab = (size_t)p->table_rows * 6 * 8, b_k0 = R * 4, b_x = 3 * R * 8, b_obs = (size_t)(3 * M) * R * 8 + 8,
                  b_sc = R * 4, b_cnt = 5 * R * 4, b_st = 3 * R * 8, b_lx = log_x ? (size_t)(T + 1) * 3 * R * 8 : 0,

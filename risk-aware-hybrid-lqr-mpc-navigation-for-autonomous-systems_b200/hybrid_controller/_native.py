@@ -58,6 +58,7 @@ SIGNATURES = {
     "b2c_destroy": (None, [_P]),
     "b2c_last_error": (C.c_char_p, []),
     "b2c_version": (C.c_int, []),
+    "b2c_current_device": (C.c_int, [C.POINTER(C.c_int)]),
     "b2c_sync": (C.c_int, [_P]),
     "b2c_stream": (_P, [_P]),
     "b2c_launch_count": (C.c_int64, [_P]),
@@ -69,6 +70,7 @@ SIGNATURES = {
     "b2c_dare_dev": (C.c_int, [_P, C.c_int64, C.c_int, C.c_int, C.c_double, _D3, _D2, _P, _P, _P, _P, _P, _P]),
     "b2c_dare_host": (C.c_int, [_P, C.c_int64, C.c_int, C.c_int, C.c_double, _D3, _D2, _P, _P, _P, _P, _P, _P]),
     "b2c_lqr_control_dev": (C.c_int, [_P, C.c_int64, C.c_double, C.c_double, _P, _P, _P, _P, _P, _P]),
+    "b2c_lqr_control_host": (C.c_int, [_P, C.c_int64, C.c_double, C.c_double, _P, _P, _P, _P, _P, _P]),
     "b2c_mpc_scratch_bytes": (C.c_int64, [C.POINTER(MpcParams), C.c_int64]),
     "b2c_mpc_dev": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
     "b2c_mpc_host": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
@@ -156,7 +158,12 @@ _default_ctx = {}
 
 
 def default_context(device=-1):
-    """Process-wide context per device for the scalar (batch = 1) drop-in calls."""
+    """Process-wide context per device for the scalar (batch = 1) drop-in calls.  device < 0 means the calling
+    thread's current CUDA device, resolved at every call: the cache is keyed by the real device id."""
+    if device < 0:
+        lib = load_library()
+        cur = C.c_int(-1)
+        device = cur.value if lib.b2c_current_device(C.byref(cur)) == 0 else -1
     ctx = _default_ctx.get(device)
     if ctx is None:
         ctx = _default_ctx[device] = Context(device)

@@ -143,23 +143,13 @@ class LQRController:
 
     def compute_control_batch(self, x, x_ref, u_ref):
         """Batched compute_control_at_operating_point: x (B,3), x_ref (B,3), u_ref (B,2) ->
-        u (B,2), wrapped error (B,3).  DARE + law on the device."""
-        import torch
+        u (B,2), wrapped error (B,3).  DARE (K2) + law on the device, host numpy in and out."""
         x = np.ascontiguousarray(x, float).reshape(-1, 3)
         B = x.shape[0]
-        dev = torch.device("cuda", torch.cuda.current_device())
-        ctx = self._ctx
-        t = lambda a, f: torch.as_tensor(np.ascontiguousarray(a, float).reshape(B, f).T.copy(), device=dev)
-        xs, xr, ur = t(x, 3), t(x_ref, 3), t(u_ref, 2)
-        K = torch.empty((6, B), dtype=torch.float64, device=dev)
-        u = torch.empty((2, B), dtype=torch.float64, device=dev)
-        e = torch.empty((3, B), dtype=torch.float64, device=dev)
-        torch.cuda.synchronize()
-        Qd, Rd = self._weights()
-        ctx.call("b2c_dare_dev", B, nat.LIN_EULER, nat.GUARD_LQR, float(self.dt),
-                 nat._D3(*map(float, Qd)), nat._D2(*map(float, Rd)),
-                 ur[0].data_ptr(), xr[2].data_ptr(), K.data_ptr(), None, None, None)
-        ctx.call("b2c_lqr_control_dev", B, float(self.v_max), float(self.omega_max),
-                 xs.data_ptr(), xr.data_ptr(), ur.data_ptr(), K.data_ptr(), u.data_ptr(), e.data_ptr())
-        ctx.sync()
-        return u.T.contiguous().cpu().numpy(), e.T.contiguous().cpu().numpy()
+        x_ref = np.ascontiguousarray(x_ref, float).reshape(B, 3)
+        u_ref = np.ascontiguousarray(u_ref, float).reshape(B, 2)
+        K, _ = self.compute_gain_batch(u_ref[:, 0], x_ref[:, 2])          # compute_gain(u_ref[0], x_ref[2]), :206
+        u, e = np.empty((B, 2)), np.empty((B, 3))
+        self._ctx.call("b2c_lqr_control_host", B, float(self.v_max), float(self.omega_max), nat._ptr(x), nat._ptr(x_ref),
+                       nat._ptr(u_ref), nat._ptr(np.ascontiguousarray(K)), nat._ptr(u), nat._ptr(e))
+        return u, e

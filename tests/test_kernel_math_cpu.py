@@ -23,7 +23,7 @@ def test_abi_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in b2c.h but not exported"
     assert declared == set(nat.SIGNATURES), declared ^ set(nat.SIGNATURES)
-    assert lib.b2c_version() == 111
+    assert lib.b2c_version() == 200
 
 
 def test_product_has_no_host_emulation_path():
