@@ -153,6 +153,24 @@ int b2c_mpc_host(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
                  double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
                  double* useq, double* xpred);
 
+/* Allocation-free variant of b2c_mpc_dev.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, layouts and results as b2c_mpc_dev run with engine = 1 (the general
+ * kernel, every problem kind / move blocking / hard rows; p->engine is ignored), but the kernel's per-instance
+ * scratch lives in a file-scope device array of 2,097,152 doubles (16 MiB, held by every GPU that loads the library
+ * until the process exits) instead of the context's arena: the call performs no cudaMalloc / cudaFree.
+ * Limit: B x scratch doubles per instance <= 2,097,152 -- b2c_mpc_static_max_instances(p) gives the largest B for a
+ * shape (4,369 for N = 20 / M = 5 / block 1; 14,563 for N = 6); a larger B is rejected with error -7 and a message.
+ * All calls on one device share the array: calls that overlap on the GPU (different streams or contexts) race, so
+ * keep them on one stream.  The array keeps the previous call's contents; nothing needs clearing (the kernel writes
+ * every field before it reads it).                                                                                  */
+int64_t b2c_mpc_static_max_instances(const b2c_mpc_params* p);
+int b2c_mpc_dev_static(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                       const double* x0, const double* xref, const double* uref, const double* obs,
+                       int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred);
+
 /* ---- closed-loop rollouts (BASELINE config 5) ------------------------------ */
 /* Replaces the reference's per-robot Python loops (run_simulation.py): run_lqr_simulation :58-96,
  * run_mpc_simulation :225-280, run_hybrid_simulation :500-570, with RiskMetrics.assess_risk

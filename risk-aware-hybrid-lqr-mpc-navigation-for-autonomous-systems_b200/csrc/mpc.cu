@@ -599,6 +599,82 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
     return 0;
 }
 
+// ---- allocation-free variant of b2c_mpc_dev (no counterpart in the reference)
+// ------------------------------------------------------------------------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// general kernel k_mpc with its per-instance scratch in a file-scope device array instead of the context's arena.
+// Every GPU that loads libb2c.so holds the array (16 MiB) until the process exits.  All calls on a device share it:
+// calls that overlap on the GPU (different streams / contexts) race.  Nothing in it has to start at zero -- the
+// kernel writes every field it later reads (linearization, inputs, gains, hard-row multipliers: mpc_solve_one's
+// setup) -- so the contents a previous call leaves behind are never observed.
+#define B2C_STATIC_SCRATCH_DOUBLES (2 * 1024 * 1024)
+static __device__ __align__(256) double g_mpc_static_scratch[B2C_STATIC_SCRATCH_DOUBLES];
+
+#ifndef B2C_HOST_EMUL
+#include <mutex>
+// In host code g_mpc_static_scratch is only a stand-in for the symbol: its device address is looked up once per
+// device, with that device current, and THAT pointer goes to the kernel.
+static int mpc_static_scratch_ptr(int device, double** out) {
+    static std::mutex mu;
+    static double* ptr[64] = {};
+    if (device < 0 || device >= 64) { b2c_set_error("static scratch: device index out of range"); return -11; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        double* q = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&q, g_mpc_static_scratch);
+        if (e != cudaSuccess) return b2c_cuda_fail(e, "cudaGetSymbolAddress(g_mpc_static_scratch)", __FILE__, __LINE__);
+        ptr[device] = q;
+    }
+    *out = ptr[device];
+    return 0;
+}
+#endif
+
+int64_t b2c_mpc_static_max_instances(const b2c_mpc_params* p) {
+    if (!p || p->N < 1 || p->M < 0) return 0;
+    return (int64_t)B2C_STATIC_SCRATCH_DOUBLES / mpc_fields(p);
+}
+
+int b2c_mpc_dev_static(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
+                       const double* x0, const double* xref, const double* uref, const double* obs,
+                       int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred) {
+#ifndef B2C_HOST_EMUL
+    if (!ctx || !p) { b2c_set_error("null context/params"); return -1; }
+    if (p->N < 1 || p->N > 4096 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
+    if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
+    if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
+    if (B <= 0) return 0;
+    const int64_t fields = mpc_fields(p);
+    if (fields * B > (int64_t)B2C_STATIC_SCRATCH_DOUBLES) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "b2c_mpc_dev_static: %lld instances x %lld scratch doubles exceed the static array "
+                 "(%d doubles = 16 MiB): at most %lld instances of this shape per call; use b2c_mpc_dev for more",
+                 (long long)B, (long long)fields, B2C_STATIC_SCRATCH_DOUBLES,
+                 (long long)((int64_t)B2C_STATIC_SCRATCH_DOUBLES / fields));
+        b2c_set_error(buf);
+        return -7;
+    }
+    B2C_DEVICE_GUARD(ctx);
+    double* scratch = nullptr;
+    int rc = mpc_static_scratch_ptr(ctx->device, &scratch);
+    if (rc) return rc;
+    MpcArgs a;
+    mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
+    a.scratch = scratch;
+    a.lam_off = (int)fields - ((!p->soft && p->M > 0) ? p->N * p->M : 0);
+    if (a.bs == 1) k_mpc<true><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    else           k_mpc<false><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    B2C_CHECK_LAUNCH(ctx);
+    return 0;
+#else
+    (void)ctx; (void)B; (void)p; (void)x0; (void)xref; (void)uref; (void)obs; (void)step_count; (void)u0; (void)cost;
+    (void)status; (void)iters; (void)slack_used; (void)useq; (void)xpred;
+    return -1;
+#endif
+}
+
 #ifdef B2C_HOST_EMUL
 #include <vector>
 // Test-only: the same per-instance solver on the host, SoA host pointers (see b2c_mpc_dev).

@@ -74,6 +74,8 @@ SIGNATURES = {
     "b2c_mpc_scratch_bytes": (C.c_int64, [C.POINTER(MpcParams), C.c_int64]),
     "b2c_mpc_dev": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
     "b2c_mpc_host": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
+    "b2c_mpc_dev_static": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
+    "b2c_mpc_static_max_instances": (C.c_int64, [C.POINTER(MpcParams)]),
     "b2c_rollout_dev": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
     "b2c_rollout_host": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
     "b2c_measure_fma_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
