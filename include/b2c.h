@@ -72,7 +72,8 @@ typedef struct {
                                  covers all multiplier rounds together)                          */
     int32_t ramp_up_steps;    /* cold-start ramp length       (:144), LTV only                  */
     int32_t engine;           /* kernel choice: 0 = automatic, 1 = general kernel (HBM scratch), 2 = persistent
-                                 slot kernel (shared-memory scratch; LTV, block_size 1, soft rows) or error -5 */
+                                 slot kernel (shared-memory + tensor-memory scratch; LTV, block_size 1, soft rows)
+                                 or error -5 */
     double  Qd[3], Rd[2], Pd[3];
     double  d_safe, rho, v_max, w_max, dt;
     double  tol;              /* relative Newton-decrement tolerance (<=0: default 1e-14)       */
@@ -152,6 +153,42 @@ int b2c_mpc_host(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
                  int32_t* step_count,
                  double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
                  double* useq, double* xpred);
+
+/* asynchronous form of b2c_mpc_host: returns as soon as the copies and kernels are enqueued; the outputs are in the
+ * caller's buffers after b2c_wait().  Staging is double-buffered: at most two calls are in flight per context (a third
+ * waits for the first), so step s+1's host->device copies overlap step s's solve.  The caller keeps every buffer of a
+ * call alive and unmodified until b2c_wait() (or until two later calls have been issued).                             */
+int b2c_mpc_host_async(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                       const double* x0, const double* xref, const double* uref, const double* obs,
+                       int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred);
+int b2c_wait(b2c_ctx*);                                       /* all asynchronous host calls have completed */
+
+/* Table form of solve_with_ltv: every instance takes its references from ONE shared table (rows,6) row-major
+ * [t,px,py,th,v,w] = ReferenceTrajectoryGenerator.generate() (HC/trajectory/reference_generator.py:196-230):
+ *     (x_refs, u_refs) of instance i = get_trajectory_segment(k0[i], N+1)                  (:299-326)
+ *                                    = rows min(k0[i] + k, rows-1), k = 0..N  (clamped at the end of the table),
+ * which is what every caller of the reference does before solve_with_ltv (run_simulation.py:247, :392, :553).  The
+ * segment is gathered on the device: 28 + 24 M bytes per instance cross PCIe instead of 24 + 40 N + 24 (N+1) + 24 M.
+ * Results are bit-identical to b2c_mpc_dev / b2c_mpc_host on the materialised segments.  kind must be B2C_MPC_LTV.
+ * dev: table, k0[B] device pointers; x0[3][B], obs[3M][B] and the outputs in the SoA layout of b2c_mpc_dev.
+ * host: x0 (B,3), obs (B,M,3), outputs as b2c_mpc_host.                                                           */
+int b2c_mpc_table_dev(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                      const double* table, int32_t table_rows, const int32_t* k0,
+                      const double* x0, const double* obs, int32_t* step_count,
+                      double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                      double* useq, double* xpred);
+int b2c_mpc_table_host(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                       const double* table, int32_t table_rows, const int32_t* k0,
+                       const double* x0, const double* obs, int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred);
+int b2c_mpc_table_host_async(b2c_ctx*, int64_t B, const b2c_mpc_params* p,
+                             const double* table, int32_t table_rows, const int32_t* k0,
+                             const double* x0, const double* obs, int32_t* step_count,
+                             double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                             double* useq, double* xpred);
 
 /* Allocation-free variant of b2c_mpc_dev.  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,

@@ -3,7 +3,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <mutex>
-#include "b2c_common.cuh"
+#include "mpc_args.cuh"
 
 static thread_local std::string g_err;
 void b2c_set_error(const std::string& s) { g_err = s; }
@@ -259,100 +259,205 @@ static int pipeline_init(b2c_ctx* c) {
     if (!c->out_stream) B2C_CUDA(cudaStreamCreateWithFlags(&c->out_stream, cudaStreamNonBlocking));
     for (int k = 0; k < 16; ++k)
         if (!c->ev[k]) B2C_CUDA(cudaEventCreateWithFlags(&c->ev[k], cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k)
+        if (!c->job[k].done) B2C_CUDA(cudaEventCreateWithFlags(&c->job[k].done, cudaEventDisableTiming));
     return 0;
 }
 
-// Host entry point of K3.  Large batches are cut into chunks of consecutive instances that flow through a
-// three-stage pipeline -- H2D copies on the context's stream, re-layout + solve on two alternating compute lanes
-// (so the tail of one chunk's persistent kernel overlaps the next chunk), D2H on an output stream -- which hides
-// most of the solve behind the PCIe transfer of the inputs (63 MB per 65,536 config-4 instances).
+// every stream a host call may have work on: drained before an error is reported, so that no copy still targets the
+// caller's buffers when the call returns
+static void pipeline_drain(b2c_ctx* c) {
+    cudaStreamSynchronize(c->stream);
+    for (int k = 0; k < 2; ++k) if (c->lane_stream[k]) cudaStreamSynchronize(c->lane_stream[k]);
+    if (c->out_stream) cudaStreamSynchronize(c->out_stream);
+    c->job[0].pending = c->job[1].pending = false;
+}
+
+int b2c_wait(b2c_ctx* c) {
+    if (!c) { b2c_set_error("null context"); return -1; }
+    B2C_DEVICE_GUARD(c);
+    for (int k = 0; k < 2; ++k)
+        if (c->job[k].pending) {
+            c->job[k].pending = false;
+            B2C_CUDA(cudaEventSynchronize(c->job[k].done));
+        }
+    return 0;
+}
+
+// Host entry of K3, both forms (materialised segments / shared table + start rows), synchronous or asynchronous.
+//
+// Staging is double-buffered per call (job 0 / 1) and the work is spread over four streams -- H2D on the context's
+// stream, solve on one of two compute lanes, D2H on an output stream -- so that (a) inside one synchronous call the
+// batch can be cut into chunks whose copies overlap the previous chunk's solve, and (b) an asynchronous call s+1
+// copies its inputs while call s is still solving.  The slot path reads the numpy-layout staging buffers as they are
+// (k_mpc_prepare gathers; outputs are written instance-major): no re-layout kernels.  The general kernel (move
+// blocking, LTI, hard rows) keeps its SoA layout and goes through the transposes, unchunked.
+static int mpc_host_impl(b2c_ctx* c, int64_t B, const b2c_mpc_params* p, const bool async,
+                         const double* table, const int table_rows, const int32_t* k0,
+                         const double* x0, const double* xref, const double* uref, const double* obs,
+                         int32_t* step_count,
+                         double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                         double* useq, double* xpred) {
+    if (!c || !p) { b2c_set_error("null context/params"); return -1; }
+    if (B <= 0) return 0;
+    if (p->N < 1 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
+    if (table && (table_rows < 1 || !k0)) { b2c_set_error("table form needs rows >= 1 and k0"); return -2; }
+    if (table && p->kind != B2C_MPC_LTV) { b2c_set_error("the table form is solve_with_ltv's (kind = B2C_MPC_LTV)"); return -2; }
+    B2C_DEVICE_GUARD(c);
+    int rc = pipeline_init(c);
+    if (rc) return rc;
+    const int N = p->N, M = p->M;
+    const int FX = 3 * (N + 1), FU = 2 * N, FO = 3 * M;
+    MpcArgs probe;
+    mpc_fill_args(probe, B, p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                  nullptr, nullptr);
+    const bool slots = mpc_uses_slots(probe, p->engine);
+    // ---- this call's staging arena (a third call in flight waits for the first) ---------------------------------
+    b2c_ctx::HostJob& job = c->job[c->job_next];
+    c->job_next ^= 1;
+    if (job.pending) { job.pending = false; B2C_CUDA(cudaEventSynchronize(job.done)); }
+    const size_t n_tab = table ? (size_t)table_rows * 6 : 0;
+    const size_t need = pad256(n_tab * 8) + pad256((size_t)B * 4) + pad256((size_t)B * 3 * 8) + 2 * pad256((size_t)B * FX * 8)
+                      + 2 * pad256((size_t)B * FU * 8) + 2 * pad256(((size_t)B * FO + 1) * 8) + pad256((size_t)B * 3 * 8)
+                      + 2 * pad256((size_t)B * 2 * 8) + pad256((size_t)B * 8) + 2 * pad256((size_t)B * FU * 8)
+                      + 2 * pad256((size_t)B * FX * 8) + 4 * pad256((size_t)B * 4) + 64 * 256;
+    rc = b2c_reserve(&job.d, &job.bytes, need, false);
+    if (rc) return rc;
+    Bump bp(job.d);
+    double* d_tab = table ? bp.take<double>(n_tab) : nullptr;
+    int32_t* d_k0 = table ? bp.take<int32_t>(B) : nullptr;
+    double* a_x0 = bp.take<double>(3 * B);
+    double* a_xr = table ? nullptr : bp.take<double>((size_t)FX * B);
+    double* a_ur = table ? nullptr : bp.take<double>((size_t)FU * B);
+    double* a_ob = bp.take<double>((size_t)FO * B + 1);
+    double* a_u0 = bp.take<double>(2 * B);
+    double* d_cost = bp.take<double>(B);
+    double* a_us = useq ? bp.take<double>((size_t)FU * B) : nullptr;
+    double* a_xp = xpred ? bp.take<double>((size_t)FX * B) : nullptr;
+    int32_t* d_sc = bp.take<int32_t>(B); int32_t* d_st = bp.take<int32_t>(B);
+    int32_t* d_it = bp.take<int32_t>(B); int32_t* d_sl = bp.take<int32_t>(B);
+    // general kernel only: the SoA twins
+    double *s_x0 = nullptr, *s_xr = nullptr, *s_ur = nullptr, *s_ob = nullptr, *s_u0 = nullptr, *s_us = nullptr, *s_xp = nullptr;
+    if (!slots) {
+        s_x0 = bp.take<double>(3 * B);
+        s_xr = table ? nullptr : bp.take<double>((size_t)FX * B);
+        s_ur = table ? nullptr : bp.take<double>((size_t)FU * B);
+        s_ob = bp.take<double>((size_t)FO * B + 1); s_u0 = bp.take<double>(2 * B);
+        s_us = useq ? bp.take<double>((size_t)FU * B) : nullptr; s_xp = xpred ? bp.take<double>((size_t)FX * B) : nullptr;
+    }
+    // ---- chunks: a multiple of 32 instances each; only a synchronous call with a large upload is cut
+    const size_t h2d = ((size_t)B * (3 + FO) + (table ? n_tab : (size_t)B * (FX + FU))) * 8;
+    int C = 1;
+    if (slots && !async && h2d >= ((size_t)24 << 20)) { C = (int)(B / 16384); if (C > 8) C = 8; if (C < 1) C = 1; }
+    if (const char* e = getenv("B2C_HOST_CHUNKS")) { int v = atoi(e); if (slots && v >= 1 && v <= 8 && B >= 64 * v) C = v; }
+    const int64_t per = C > 1 ? ((B / C + 31) / 32) * 32 : B;
+    cudaStream_t s_in = c->stream;
+    cudaError_t ce = cudaSuccess;
+#define HOSTCP(dst, src, bytes, kind, st) \
+    do { if (ce == cudaSuccess && (bytes) > 0) ce = cudaMemcpyAsync((dst), (src), (bytes), (kind), (st)); } while (0)
+    if (table) {
+        HOSTCP(d_tab, table, n_tab * 8, cudaMemcpyHostToDevice, s_in);
+        HOSTCP(d_k0, k0, (size_t)B * 4, cudaMemcpyHostToDevice, s_in);
+    }
+    for (int ch = 0; ch < C && rc == 0 && ce == cudaSuccess; ++ch) {
+        const int64_t i0 = (int64_t)ch * per, Bc = (ch == C - 1) ? B - i0 : per;
+        if (Bc <= 0) break;
+        HOSTCP(a_x0 + 3 * i0, x0 + 3 * i0, (size_t)Bc * 3 * 8, cudaMemcpyHostToDevice, s_in);
+        if (!table) {
+            HOSTCP(a_xr + FX * i0, xref + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyHostToDevice, s_in);
+            HOSTCP(a_ur + FU * i0, uref + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyHostToDevice, s_in);
+        }
+        if (FO) HOSTCP(a_ob + FO * i0, obs + FO * i0, (size_t)Bc * FO * 8, cudaMemcpyHostToDevice, s_in);
+        if (step_count) HOSTCP(d_sc + i0, step_count + i0, (size_t)Bc * 4, cudaMemcpyHostToDevice, s_in);
+        if (ce != cudaSuccess) break;
+        const int lane = (int)(c->chunk_seq++ & 1);
+        ce = cudaEventRecord(c->ev[ch], s_in);
+        if (ce == cudaSuccess) ce = cudaStreamWaitEvent(c->lane_stream[lane], c->ev[ch], 0);
+        if (ce != cudaSuccess) break;
+        {
+            LaneScope scope(c, lane);
+            if (slots) {
+                MpcArgs a;
+                mpc_fill_args(a, Bc, p, a_x0 + 3 * i0, table ? nullptr : a_xr + FX * i0, table ? nullptr : a_ur + FU * i0,
+                              a_ob + FO * i0, step_count ? d_sc + i0 : nullptr, a_u0 + 2 * i0, d_cost + i0, d_st + i0,
+                              d_it + i0, d_sl + i0, useq ? a_us + FU * i0 : nullptr, xpred ? a_xp + FX * i0 : nullptr);
+                a.in_aos = 1; a.out_aos = 1;
+                if (table) { a.table = d_tab; a.table_rows = table_rows; a.k0 = d_k0 + i0; }
+                rc = mpc_launch(c, a, p->engine);
+            } else {                                  // C == 1: the whole batch through the transposes
+                if (rc == 0) rc = to_soa(c, B, 3, a_x0, s_x0);
+                if (rc == 0 && !table) rc = to_soa(c, B, FX, a_xr, s_xr);
+                if (rc == 0 && !table) rc = to_soa(c, B, FU, a_ur, s_ur);
+                if (rc == 0) rc = to_soa(c, B, FO, a_ob, s_ob);
+                if (rc == 0)
+                    rc = table ? b2c_mpc_table_dev(c, B, p, d_tab, table_rows, d_k0, s_x0, s_ob, step_count ? d_sc : nullptr,
+                                                   s_u0, d_cost, d_st, d_it, d_sl, s_us, s_xp)
+                               : b2c_mpc_dev(c, B, p, s_x0, s_xr, s_ur, s_ob, step_count ? d_sc : nullptr,
+                                             s_u0, d_cost, d_st, d_it, d_sl, s_us, s_xp);
+                if (rc == 0) rc = to_aos(c, B, 2, s_u0, a_u0);
+                if (rc == 0 && useq) rc = to_aos(c, B, FU, s_us, a_us);
+                if (rc == 0 && xpred) rc = to_aos(c, B, FX, s_xp, a_xp);
+            }
+            if (rc == 0) ce = cudaEventRecord(c->ev[8 + ch], c->stream);
+        }
+        if (rc || ce != cudaSuccess) break;
+        cudaStream_t s_out = c->out_stream;
+        ce = cudaStreamWaitEvent(s_out, c->ev[8 + ch], 0);
+        HOSTCP(u0 + 2 * i0, a_u0 + 2 * i0, (size_t)Bc * 2 * 8, cudaMemcpyDeviceToHost, s_out);
+        HOSTCP(cost + i0, d_cost + i0, (size_t)Bc * 8, cudaMemcpyDeviceToHost, s_out);
+        if (useq) HOSTCP(useq + FU * i0, a_us + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyDeviceToHost, s_out);
+        if (xpred) HOSTCP(xpred + FX * i0, a_xp + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyDeviceToHost, s_out);
+        if (status) HOSTCP(status + i0, d_st + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out);
+        if (iters) HOSTCP(iters + i0, d_it + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out);
+        if (slack_used) HOSTCP(slack_used + i0, d_sl + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out);
+        if (step_count) HOSTCP(step_count + i0, d_sc + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out);
+    }
+#undef HOSTCP
+    if (rc == 0 && ce == cudaSuccess) ce = cudaEventRecord(job.done, c->out_stream);
+    if (rc || ce != cudaSuccess) {                    // nothing may still be in flight when an error is reported
+        const std::string msg = b2c_last_error();
+        pipeline_drain(c);
+        if (rc) { b2c_set_error(msg); return rc; }
+        return b2c_cuda_fail(ce, "host pipeline", __FILE__, __LINE__);
+    }
+    if (async) { job.pending = true; return 0; }
+    B2C_CUDA(cudaEventSynchronize(job.done));
+    return 0;
+}
+
 int b2c_mpc_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
                  const double* x0, const double* xref, const double* uref, const double* obs,
                  int32_t* step_count,
                  double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
                  double* useq, double* xpred) {
-    if (!c || !p) { b2c_set_error("null context/params"); return -1; }
-    if (B <= 0) return 0;
-    if (p->N < 1 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
-    B2C_DEVICE_GUARD(c);
-    const int N = p->N, M = p->M;
-    const int FX = 3 * (N + 1), FU = 2 * N, FO = 3 * M;
-    const size_t nin = (size_t)B * (3 + FX + FU + FO);
-    const size_t nout = (size_t)B * (2 + 1 + (useq ? FU : 0) + (xpred ? FX : 0));
-    size_t need = 2 * pad256(nin * 8) + 2 * pad256(nout * 8) + 16 * 256 + 4 * pad256(B * 4) + 8 * 256 * 4;
-    int rc = b2c_reserve(&c->dstage, &c->dstage_bytes, need, false);
-    if (rc) return rc;
-    Bump bp(c->dstage);
-    double* a_x0 = bp.take<double>(3 * B);   double* s_x0 = bp.take<double>(3 * B);
-    double* a_xr = bp.take<double>(FX * B);  double* s_xr = bp.take<double>(FX * B);
-    double* a_ur = bp.take<double>(FU * B);  double* s_ur = bp.take<double>(FU * B);
-    double* a_ob = bp.take<double>(FO * B + 1); double* s_ob = bp.take<double>(FO * B + 1);
-    double* s_u0 = bp.take<double>(2 * B);   double* a_u0 = bp.take<double>(2 * B);
-    double* d_cost = bp.take<double>(B);
-    double* s_us = useq ? bp.take<double>(FU * B) : nullptr;  double* a_us = useq ? bp.take<double>(FU * B) : nullptr;
-    double* s_xp = xpred ? bp.take<double>(FX * B) : nullptr; double* a_xp = xpred ? bp.take<double>(FX * B) : nullptr;
-    int32_t* d_sc = bp.take<int32_t>(B); int32_t* d_st = bp.take<int32_t>(B);
-    int32_t* d_it = bp.take<int32_t>(B); int32_t* d_sl = bp.take<int32_t>(B);
-    // chunks: a multiple of 32 instances each, at most 8, none smaller than 8,192 instances
-    int C = (int)(B / 16384);
-    if (C > 8) C = 8;
-    if (C < 2) C = 1;
-    if (const char* e = getenv("B2C_HOST_CHUNKS")) { int v = atoi(e); if (v >= 1 && v <= 8 && B >= 64 * v) C = v; }
-    if (C > 1 && (rc = pipeline_init(c))) return rc;
-    const int64_t per = C > 1 ? ((B / C + 31) / 32) * 32 : B;
-    cudaStream_t s_in = c->stream;
-    for (int ch = 0; ch < C; ++ch) {
-        const int64_t i0 = (int64_t)ch * per, Bc = (ch == C - 1) ? B - i0 : per;
-        if (Bc <= 0) break;
-        // chunk-local SoA blocks sit at offset F*i0 of the full-size buffers (sum of F*Bc over chunks = F*B)
-        double* cx0 = s_x0 + 3 * i0; double* cxr = s_xr + (int64_t)FX * i0; double* cur = s_ur + (int64_t)FU * i0;
-        double* cob = s_ob + (int64_t)FO * i0; double* cu0 = s_u0 + 2 * i0;
-        double* cus = useq ? s_us + (int64_t)FU * i0 : nullptr; double* cxp = xpred ? s_xp + (int64_t)FX * i0 : nullptr;
-        B2C_CUDA(cudaMemcpyAsync(a_x0 + 3 * i0, x0 + 3 * i0, (size_t)Bc * 3 * 8, cudaMemcpyHostToDevice, s_in));
-        B2C_CUDA(cudaMemcpyAsync(a_xr + FX * i0, xref + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyHostToDevice, s_in));
-        B2C_CUDA(cudaMemcpyAsync(a_ur + FU * i0, uref + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyHostToDevice, s_in));
-        if (FO) B2C_CUDA(cudaMemcpyAsync(a_ob + FO * i0, obs + FO * i0, (size_t)Bc * FO * 8, cudaMemcpyHostToDevice, s_in));
-        if (step_count) B2C_CUDA(cudaMemcpyAsync(d_sc + i0, step_count + i0, (size_t)Bc * 4, cudaMemcpyHostToDevice, s_in));
-        cudaStream_t s_out = s_in;
-        {
-            const int lane = ch & 1;
-            if (C > 1) {
-                B2C_CUDA(cudaEventRecord(c->ev[ch], s_in));
-                B2C_CUDA(cudaStreamWaitEvent(c->lane_stream[lane], c->ev[ch], 0));
-            }
-            struct Maybe { LaneScope* l; ~Maybe() { delete l; } } scope{C > 1 ? new LaneScope(c, lane) : nullptr};
-            if ((rc = to_soa(c, Bc, 3, a_x0 + 3 * i0, cx0))) return rc;
-            if ((rc = to_soa(c, Bc, FX, a_xr + FX * i0, cxr))) return rc;
-            if ((rc = to_soa(c, Bc, FU, a_ur + FU * i0, cur))) return rc;
-            if ((rc = to_soa(c, Bc, FO, a_ob + FO * i0, cob))) return rc;
-            rc = b2c_mpc_dev(c, Bc, p, cx0, cxr, cur, cob, step_count ? d_sc + i0 : nullptr,
-                             cu0, d_cost + i0, d_st + i0, d_it + i0, d_sl + i0, cus, cxp);
-            if (rc) return rc;
-            if ((rc = to_aos(c, Bc, 2, cu0, a_u0 + 2 * i0))) return rc;
-            if (useq && (rc = to_aos(c, Bc, FU, cus, a_us + FU * i0))) return rc;
-            if (xpred && (rc = to_aos(c, Bc, FX, cxp, a_xp + FX * i0))) return rc;
-            if (C > 1) {
-                B2C_CUDA(cudaEventRecord(c->ev[8 + ch], c->stream));
-                B2C_CUDA(cudaStreamWaitEvent(c->out_stream, c->ev[8 + ch], 0));
-                s_out = c->out_stream;
-            }
-        }
-        B2C_CUDA(cudaMemcpyAsync(u0 + 2 * i0, a_u0 + 2 * i0, (size_t)Bc * 2 * 8, cudaMemcpyDeviceToHost, s_out));
-        B2C_CUDA(cudaMemcpyAsync(cost + i0, d_cost + i0, (size_t)Bc * 8, cudaMemcpyDeviceToHost, s_out));
-        if (useq) B2C_CUDA(cudaMemcpyAsync(useq + FU * i0, a_us + FU * i0, (size_t)Bc * FU * 8, cudaMemcpyDeviceToHost, s_out));
-        if (xpred) B2C_CUDA(cudaMemcpyAsync(xpred + FX * i0, a_xp + FX * i0, (size_t)Bc * FX * 8, cudaMemcpyDeviceToHost, s_out));
-        if (status) B2C_CUDA(cudaMemcpyAsync(status + i0, d_st + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
-        if (iters) B2C_CUDA(cudaMemcpyAsync(iters + i0, d_it + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
-        if (slack_used) B2C_CUDA(cudaMemcpyAsync(slack_used + i0, d_sl + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
-        if (step_count) B2C_CUDA(cudaMemcpyAsync(step_count + i0, d_sc + i0, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s_out));
-    }
-    if (C > 1) {
-        B2C_CUDA(cudaStreamSynchronize(c->out_stream));
-        B2C_CUDA(cudaStreamSynchronize(c->lane_stream[0]));
-        B2C_CUDA(cudaStreamSynchronize(c->lane_stream[1]));
-    }
-    B2C_CUDA(cudaStreamSynchronize(s_in));
-    return 0;
+    return mpc_host_impl(c, B, p, false, nullptr, 0, nullptr, x0, xref, uref, obs, step_count, u0, cost, status, iters,
+                         slack_used, useq, xpred);
+}
+int b2c_mpc_host_async(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
+                       const double* x0, const double* xref, const double* uref, const double* obs,
+                       int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred) {
+    return mpc_host_impl(c, B, p, true, nullptr, 0, nullptr, x0, xref, uref, obs, step_count, u0, cost, status, iters,
+                         slack_used, useq, xpred);
+}
+int b2c_mpc_table_host(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
+                       const double* table, int32_t table_rows, const int32_t* k0,
+                       const double* x0, const double* obs, int32_t* step_count,
+                       double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                       double* useq, double* xpred) {
+    if (!table) { b2c_set_error("null table"); return -1; }
+    return mpc_host_impl(c, B, p, false, table, table_rows, k0, x0, nullptr, nullptr, obs, step_count, u0, cost, status,
+                         iters, slack_used, useq, xpred);
+}
+int b2c_mpc_table_host_async(b2c_ctx* c, int64_t B, const b2c_mpc_params* p,
+                             const double* table, int32_t table_rows, const int32_t* k0,
+                             const double* x0, const double* obs, int32_t* step_count,
+                             double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                             double* useq, double* xpred) {
+    if (!table) { b2c_set_error("null table"); return -1; }
+    return mpc_host_impl(c, B, p, true, table, table_rows, k0, x0, nullptr, nullptr, obs, step_count, u0, cost, status,
+                         iters, slack_used, useq, xpred);
 }
 
 // ---- FMA peak microbenchmark (FP64 / FP32 roofline denominators) ------------------------------

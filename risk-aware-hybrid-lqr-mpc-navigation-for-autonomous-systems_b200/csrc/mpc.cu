@@ -14,6 +14,7 @@
 // gradient are frozen) + a forward roll-out with feedback, clipping and a monotone line search.
 // When the active sets stop changing the step lands on the exact minimiser (to rounding), i.e. the
 // same point CVXPY/OSQP approximates to 1e-5; typical count is 1-8 iterations.
+#include <string.h>
 #include "mpc_args.cuh"
 
 namespace {
@@ -542,7 +543,7 @@ template <bool BS1>
 __global__ void __launch_bounds__(MPC_TPB)
 k_mpc(const MpcArgs a) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < a.B) mpc_solve_one<BS1>(a, i);
+    if (i < mpc_count(a)) mpc_solve_one<BS1>(a, i);
 }
 
 }  // namespace
@@ -561,11 +562,46 @@ int64_t b2c_mpc_scratch_bytes(const b2c_mpc_params* p, int64_t B) {
                   nullptr, nullptr);
     int tpb = 0;
     if (p->engine != B2C_MPC_ENGINE_GENERAL && mpc_slots_eligible(a, &tpb)) {
-        // slot kernel: G[6N] + GG[8N] doubles per RESIDENT slot (one CTA per SM, 148 SMs assumed here)
-        int64_t slots = (B + tpb - 1) / tpb; if (slots > 2 * 148) slots = 2 * 148;   // upper bound
-        return (int64_t)14 * p->N * slots * tpb * (int64_t)sizeof(double) + 256;
+        int dev = 0, sms = 148;                       // the device the calling thread is on (informational figure)
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        return mpc_slots_scratch_bytes(a, sms);
     }
     return (int64_t)mpc_fields(p) * B * (int64_t)sizeof(double);
+}
+
+static int mpc_check_params(const b2c_mpc_params* p) {
+    if (p->N < 1 || p->N > 4096 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
+    if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
+    if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
+    return 0;
+}
+
+bool mpc_uses_slots(const MpcArgs& a, int engine) {
+    int tpb = 0;
+    return engine != B2C_MPC_ENGINE_GENERAL && mpc_slots_eligible(a, &tpb);
+}
+
+int mpc_launch(b2c_ctx* ctx, MpcArgs& a, int engine) {
+    int tpb = 0;
+    const bool slots_ok = mpc_slots_eligible(a, &tpb);
+    if (engine == B2C_MPC_ENGINE_SLOTS && !slots_ok) {
+        b2c_set_error("slot kernel needs kind=LTV, block_size=1, soft rows and a horizon whose strips fit one SM");
+        return -5;
+    }
+    if (slots_ok && engine != B2C_MPC_ENGINE_GENERAL) return mpc_slots_launch(ctx, a, tpb);
+    if (a.in_aos || a.out_aos || a.table) { b2c_set_error("internal: the general kernel takes SoA buffers"); return -6; }
+    b2c_mpc_params pp;
+    memset(&pp, 0, sizeof pp);
+    pp.kind = a.kind; pp.N = a.N; pp.M = a.M; pp.block_size = a.bs; pp.soft = a.soft;
+    const size_t need = (size_t)mpc_fields(&pp) * (size_t)a.B * sizeof(double);
+    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, need, false);
+    if (rc) return rc;
+    a.scratch = (double*)ctx->scratch;
+    a.lam_off = mpc_fields(&pp) - ((!a.soft && a.M > 0) ? a.N * a.M : 0);
+    if (a.bs == 1) k_mpc<true><<<b2c_blocks(a.B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    else           k_mpc<false><<<b2c_blocks(a.B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    B2C_CHECK_LAUNCH(ctx);
+    return 0;
 }
 
 int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
@@ -574,29 +610,58 @@ int b2c_mpc_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
                 double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
                 double* useq, double* xpred) {
     if (!ctx || !p) { b2c_set_error("null context/params"); return -1; }
-    if (p->N < 1 || p->N > 4096 || p->M < 0) { b2c_set_error("bad horizon / obstacle count"); return -2; }
-    if (p->kind != B2C_MPC_LTV && p->kind != B2C_MPC_LTI) { b2c_set_error("bad MPC kind"); return -2; }
-    if (!(p->Rd[0] > 0) || !(p->Rd[1] > 0)) { b2c_set_error("R must be positive definite"); return -3; }
+    int rc = mpc_check_params(p);
+    if (rc) return rc;
     if (B <= 0) return 0;
     B2C_DEVICE_GUARD(ctx);
     MpcArgs a;
     mpc_fill_args(a, B, p, x0, xref, uref, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
-    int tpb = 0;
-    const bool slots_ok = mpc_slots_eligible(a, &tpb);
-    if (p->engine == B2C_MPC_ENGINE_SLOTS && !slots_ok) {
-        b2c_set_error("slot kernel needs kind=LTV, block_size=1, soft rows and 10N+3M <= 896");
-        return -5;
+    return mpc_launch(ctx, a, p->engine);
+}
+
+// (x_refs, u_refs) of instance i = rows min(k0[i] + k, rows - 1) of the shared table -> instance-minor SoA (only the
+// general kernel needs them materialised; the slot path gathers inside k_mpc_prepare)
+__global__ void __launch_bounds__(256)
+k_mpc_table_gather(const MpcArgs a, double* __restrict__ xref, double* __restrict__ uref) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, B = a.B;
+    if (i >= mpc_count(a)) return;
+    for (int k = 0; k <= a.N; ++k) {
+        const double* row = a.table + (int64_t)mpc_table_row(a, i, k) * 6;
+        xref[(int64_t)(3 * k) * B + i] = row[1]; xref[(int64_t)(3 * k + 1) * B + i] = row[2];
+        xref[(int64_t)(3 * k + 2) * B + i] = row[3];
+        if (k < a.N) { uref[(int64_t)(2 * k) * B + i] = row[4]; uref[(int64_t)(2 * k + 1) * B + i] = row[5]; }
     }
-    if (slots_ok && p->engine != B2C_MPC_ENGINE_GENERAL) return mpc_slots_launch(ctx, a, tpb);
-    const size_t need = (size_t)mpc_fields(p) * (size_t)B * sizeof(double);
-    int rc = b2c_reserve(&ctx->scratch, &ctx->scratch_bytes, need, false);
+}
+
+// table form with SoA x0 / obs / outputs (`a.table`, `a.table_rows`, `a.k0` set by the caller)
+int mpc_table_launch(b2c_ctx* ctx, MpcArgs& a, int engine) {
+    if (mpc_uses_slots(a, engine)) return mpc_launch(ctx, a, engine);
+    const size_t nx = (size_t)3 * (a.N + 1) * a.B, nu = (size_t)2 * a.N * a.B;
+    int rc = b2c_reserve(&ctx->aux, &ctx->aux_bytes, (nx + nu) * sizeof(double), false);
     if (rc) return rc;
-    a.scratch = (double*)ctx->scratch;
-    a.lam_off = mpc_fields(p) - ((!p->soft && p->M > 0) ? p->N * p->M : 0);
-    if (a.bs == 1) k_mpc<true><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
-    else           k_mpc<false><<<b2c_blocks(B, MPC_TPB), MPC_TPB, 0, ctx->stream>>>(a);
+    double* xr = (double*)ctx->aux; double* ur = xr + nx;
+    k_mpc_table_gather<<<b2c_blocks(a.B, 256), 256, 0, ctx->stream>>>(a, xr, ur);
     B2C_CHECK_LAUNCH(ctx);
-    return 0;
+    a.xref = xr; a.uref = ur; a.table = nullptr; a.k0 = nullptr; a.table_rows = 0;
+    return mpc_launch(ctx, a, engine);
+}
+
+int b2c_mpc_table_dev(b2c_ctx* ctx, int64_t B, const b2c_mpc_params* p,
+                      const double* table, int32_t table_rows, const int32_t* k0,
+                      const double* x0, const double* obs, int32_t* step_count,
+                      double* u0, double* cost, int32_t* status, int32_t* iters, int32_t* slack_used,
+                      double* useq, double* xpred) {
+    if (!ctx || !p || !table || !k0) { b2c_set_error("null context/params/table"); return -1; }
+    int rc = mpc_check_params(p);
+    if (rc) return rc;
+    if (table_rows < 1) { b2c_set_error("empty reference table"); return -2; }
+    if (p->kind != B2C_MPC_LTV) { b2c_set_error("the table form is solve_with_ltv's (kind = B2C_MPC_LTV)"); return -2; }
+    if (B <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
+    MpcArgs a;
+    mpc_fill_args(a, B, p, x0, nullptr, nullptr, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred);
+    a.table = table; a.table_rows = table_rows; a.k0 = k0;
+    return mpc_table_launch(ctx, a, p->engine);
 }
 
 // ---- allocation-free variant of b2c_mpc_dev (no counterpart in the reference; added

@@ -74,6 +74,12 @@ SIGNATURES = {
     "b2c_mpc_scratch_bytes": (C.c_int64, [C.POINTER(MpcParams), C.c_int64]),
     "b2c_mpc_dev": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
     "b2c_mpc_host": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
+    "b2c_mpc_host_async": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
+    "b2c_wait": (C.c_int, [_P]),
+    # table form: (ctx, B, params, table, rows, k0, x0, obs, step_count, u0, cost, status, iters, slack_used, useq, xpred)
+    "b2c_mpc_table_dev": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams), _P, C.c_int32] + [_P] * 11),
+    "b2c_mpc_table_host": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams), _P, C.c_int32] + [_P] * 11),
+    "b2c_mpc_table_host_async": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams), _P, C.c_int32] + [_P] * 11),
     "b2c_mpc_dev_static": (C.c_int, [_P, C.c_int64, C.POINTER(MpcParams)] + [_P] * 12),
     "b2c_mpc_static_max_instances": (C.c_int64, [C.POINTER(MpcParams)]),
     "b2c_rollout_dev": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
