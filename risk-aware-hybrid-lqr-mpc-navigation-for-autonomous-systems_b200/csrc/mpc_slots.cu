@@ -284,6 +284,7 @@ B2C_HD void slot_row(const MpcArgs& a, double ddx, double ddy, double d2, double
 // ----- forward sweep -------------------------------------------------------------------------------
 // Every lane of the warp runs it; `act` lanes are the ones whose result counts (the others compute on stale strips).
 // fresh: first evaluation of a new instance, w = clip(0) (written to W).
+// any_gain: some lane of the warp runs a gain sweep (warp-uniform: decides whether the gains are loaded at all).
 // gain : w+ = clip(w - alpha*kf - K (z+ - z)), rolled out closed loop; W is updated IN PLACE, the previous inputs
 //        go to the slot's global strip GW (the model overwrites the gains it just used).
 // Obstacle rows: row (k,m) is violated iff  c*dist > q  with  q = d2 + dd.dz  (both sides of
@@ -291,7 +292,7 @@ B2C_HD void slot_row(const MpcArgs& a, double ddx, double ddy, double d2, double
 // stage are independent (they pipeline); only rows that pass take the rsqrt path.
 template <int SS, int MT, int KT>
 B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x, const double z0y, const double z0t,
-                           const double alpha_, const bool act, const bool gain, const bool fresh,
+                           const double alpha_, const bool act, const bool gain, const bool fresh, const bool any_gain,
                            double& max_viol, double& lamx, double& lamy, double& lamt) {
     const int N = a.N, M = (MT >= 0) ? MT : a.M;
     constexpr int MR = (MT > 0) ? MT : 1;
@@ -313,8 +314,8 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         const Stage6 cur = ring_take<SS>(m, k);
         const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1, prx = cur.prx, pry = cur.pry;
         ring_issue<SS>(m, k + 2, act && k + 2 < N, ck + pry);       // constants two stages ahead
-        double u[8];
-        u_load8<SS, KT>(m, k, u);                     // the gains of this stage (gain sweeps)
+        double u[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (any_gain) u_load8<SS, KT>(m, k, u);       // the gains of this stage (any_gain: warp-uniform)
         const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
         const double wo0 = fresh ? b2c_clip(0.0, lb0, ub0) : MW(2 * k);
         const double wo1 = fresh ? b2c_clip(0.0, lb1, ub1) : MW(2 * k + 1);
@@ -479,31 +480,49 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
 template <int SS, int KT>
 B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred, const bool open_loop) {
     const int N = a.N;
+    constexpr int C = 4;                              // stages whose mirror / record loads are in flight together: one L2
+                                                      // round trip per four stages instead of one per stage
     double dx = 0.0, dy = 0.0, dth = 0.0;
-    for (int j = 0; j < N; ++j) {
-        double u[8];
-        u_load8<SS, KT>(m, j, u);
-        if (pred) {
-            const double2 wp = *reinterpret_cast<const double2*>(m.gw + (int64_t)j * 2 * m.gs);
-            const double2* p = reinterpret_cast<const double2*>(m.gg + (int64_t)j * 8 * m.gs);
-            const double2 q0 = p[0], q1 = p[1], q2 = p[2], q3 = p[3];
-            MW(2 * j) = wp.x; MW(2 * j + 1) = wp.y;
-            u[0] = q0.x; u[1] = q0.y; u[2] = q1.x; u[3] = q1.y; u[4] = q2.x; u[5] = q2.y; u[6] = q3.x; u[7] = q3.y;
-        }
-        if (open_loop) {
-            double ck, sk, uo0, uo1;
-            g_load4(m, j, ck, sk, uo0, uo1);
-            const double d0 = -u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
-            const double d1 = -u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
-            const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
-            const double ndx = dx + (-vr * sk) * dth + ck * d0;
-            const double ndy = dy + (vr * ck) * dth + sk * d0;
-            dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+    for (int j0 = 0; j0 < N; j0 += C) {
+        double2 wp[C], q0[C], q1[C], q2[C], q3[C];
+        double ck[C], sk[C], uo0[C], uo1[C];
 #pragma unroll
-            for (int e = 0; e < 6; ++e) u[e] = 0.0;
-            u[6] = -d0; u[7] = -d1;
+        for (int c = 0; c < C; ++c) {
+            const int j = (j0 + c < N) ? (j0 + c) : (N - 1);
+            wp[c] = q0[c] = q1[c] = q2[c] = q3[c] = make_double2(0.0, 0.0);
+            ck[c] = sk[c] = uo0[c] = uo1[c] = 0.0;
+            if (pred) {
+                wp[c] = *reinterpret_cast<const double2*>(m.gw + (int64_t)j * 2 * m.gs);
+                const double2* p = reinterpret_cast<const double2*>(m.gg + (int64_t)j * 8 * m.gs);
+                q0[c] = p[0]; q1[c] = p[1]; q2[c] = p[2]; q3[c] = p[3];
+            }
+            if (open_loop) g_load4(m, j, ck[c], sk[c], uo0[c], uo1[c]);
         }
-        u_store8<SS, KT>(m, j, u);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const int j = j0 + c;
+            if (j < N) {
+                double u[8];
+                u_load8<SS, KT>(m, j, u);
+                if (pred) {
+                    MW(2 * j) = wp[c].x; MW(2 * j + 1) = wp[c].y;
+                    u[0] = q0[c].x; u[1] = q0[c].y; u[2] = q1[c].x; u[3] = q1[c].y;
+                    u[4] = q2[c].x; u[5] = q2[c].y; u[6] = q3[c].x; u[7] = q3[c].y;
+                }
+                if (open_loop) {
+                    const double d0 = -u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
+                    const double d1 = -u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
+                    const double vr = b2c_guard_v(uo0[c], B2C_GUARD_MPC);
+                    const double ndx = dx + (-vr * sk[c]) * dth + ck[c] * d0;
+                    const double ndy = dy + (vr * ck[c]) * dth + sk[c] * d0;
+                    dth = dth + a.dt * d1; dx = ndx; dy = ndy;
+#pragma unroll
+                    for (int e = 0; e < 6; ++e) u[e] = 0.0;
+                    u[6] = -d0; u[7] = -d1;
+                }
+                u_store8<SS, KT>(m, j, u);
+            }
+        }
     }
     u_fence<KT>();
 }
@@ -868,7 +887,8 @@ k_mpc_slots(const MpcArgs a) {
         const bool run = gain || plain || helper;
         const bool fgain = gain || helper;
         double Jn = 0.0, mv = 0.0, lx = 0.0, ly = 0.0, lt = 0.0;
-        if (__any_sync(FULL, run)) Jn = slot_forward<SS, MT, KT>(a, m, fz0x, fz0y, fz0t, falpha, run, fgain, plain, mv, lx, ly, lt);
+        if (__any_sync(FULL, run))
+            Jn = slot_forward<SS, MT, KT>(a, m, fz0x, fz0y, fz0t, falpha, run, fgain, plain, __any_sync(FULL, fgain), mv, lx, ly, lt);
         __syncwarp();
         int krej = 1;
         bool handled = false;                                             // my instance moved to a helper's lane
@@ -925,28 +945,39 @@ k_mpc_slots(const MpcArgs a) {
 }  // namespace
 
 // ----- launch configuration ---------------------------------------------------------------------------
-// (threads per CTA, U stages in tensor memory), in order of preference: 256 slots per SM with all strips in shared
-// memory (short horizons), 256 slots with the first 16 stages of U in TMEM (N <= 21 at M = 5: the shape of BASELINE
-// config 4), 128 slots in shared memory, 128 slots with 32 stages in TMEM, then 64 / 32 slots for very long horizons.
+// (slots per CTA, U stages in tensor memory).  Measured on config 4 (N = 20, M = 5; profiles/r2_*):
+//   * 256 slots per SM with the first 16 stages of U in TMEM is the THROUGHPUT configuration: two warps per scheduler,
+//     1.47x the sweeps per SM and second, 288 M solves/s at 1,048,576 instances against 239 M with 128 slots -- but
+//     every round of a warp is 36 % longer, and at 65,536 instances (1.7 instances per slot) the makespan is the
+//     latency of the hardest instances, 13 Newton iterations one round each: 0.57 ms against 0.45.
+//   * so: TMEM only when the batch fills the resident slots several times over (B >= 4 x SMs x 256), otherwise the
+//     largest CTA that still spreads the batch over all SMs (a 4,096-instance batch runs as 128 CTAs of 32 slots, one
+//     warp alone on its SM, not as 16 CTAs of 256).
+//   * short horizons (N <= 8 at M = 3: the closed-loop rollouts) fit 256 slots per SM in shared memory alone.
 namespace {
 struct SlotCfg { int tpb, kt; size_t smem; };
 const size_t SLOT_SMEM_CAP = 227 * 1024;
 size_t slot_cfg_smem(const MpcArgs& a, int tpb, int kt) {
     return (size_t)(slot_fields(a, kt) + 12) * tpb * sizeof(double) + (kt > 0 ? 16 : 0);
 }
-bool slot_pick(const MpcArgs& a, SlotCfg* out) {
+bool slot_pick(const MpcArgs& a, SlotCfg* out, int sm_count = 148) {
     if (a.kind != B2C_MPC_LTV || a.bs != 1 || !a.soft) return false;
-    static const int cand[6][2] = {{256, 0}, {256, 16}, {128, 0}, {128, 32}, {64, 0}, {32, 0}};
+    static const int cand[7][2] = {{256, 0}, {256, 16}, {128, 0}, {128, 32}, {64, 0}, {64, 32}, {32, 0}};
     int ftpb = 0, fkt = -1;                           // B2C_SLOTS_CFG="tpb,kt": developer override for A/B measurements
     if (const char* e = getenv("B2C_SLOTS_CFG")) sscanf(e, "%d,%d", &ftpb, &fkt);
-    for (int pass = 0; pass < 2; ++pass) {
-        for (int c = 0; c < 6; ++c) {
+    const bool throughput = a.B >= (int64_t)4 * sm_count * 256;
+    // largest CTA that still gives every SM one: B >= sm_count * tpb (32 at least)
+    int max_tpb = 256;
+    while (max_tpb > 32 && a.B < (int64_t)sm_count * max_tpb) max_tpb >>= 1;
+    for (int pass = ftpb ? 0 : 1; pass < 3; ++pass) {
+        // pass 0: the override only; pass 1: the policy above; pass 2: anything that fits
+        for (int c = 0; c < 7; ++c) {
             const int tpb = cand[c][0], kt = cand[c][1];
-            if (pass == 0 && ftpb && (tpb != ftpb || kt != fkt)) continue;
+            if (pass == 0 && (tpb != ftpb || kt != fkt)) continue;
+            if (pass == 1 && (tpb > max_tpb || (kt > 0 && tpb == 256 && !throughput))) continue;
             const size_t smem = slot_cfg_smem(a, tpb, kt);
             if (smem <= SLOT_SMEM_CAP) { out->tpb = tpb; out->kt = kt; out->smem = smem; return true; }
         }
-        if (!ftpb) break;                             // no override: one pass
     }
     return false;
 }
@@ -976,7 +1007,7 @@ static bool slot_ordered(const MpcArgs& a, int64_t nslots) { return a.M > 0 && a
 
 int64_t mpc_slots_scratch_bytes(const MpcArgs& a, int sm_count) {
     SlotCfg c;
-    if (!slot_pick(a, &c)) return 0;
+    if (!slot_pick(a, &c, sm_count)) return 0;
     const int64_t nslots = slot_resident(a, c, sm_count);
     size_t strips, recs, perm;
     slot_scratch_layout(a, nslots, slot_ordered(a, nslots), &strips, &recs, &perm);
@@ -1002,7 +1033,7 @@ static int slots_launch_m(b2c_ctx* ctx, const MpcArgs& a, int grid, size_t smem)
 
 int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int) {
     SlotCfg c;
-    if (!slot_pick(a, &c)) { b2c_set_error("slot kernel: shape not eligible"); return -5; }
+    if (!slot_pick(a, &c, ctx->sm_count)) { b2c_set_error("slot kernel: shape not eligible"); return -5; }
     a.nslots = slot_resident(a, c, ctx->sm_count);
     const int grid = (int)(a.nslots / c.tpb);
     // a kernel that allocates all of an SM's tensor memory must be alone on that SM (a second CTA would wait for
@@ -1036,8 +1067,9 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int) {
     if (c.tpb == 256 && c.kt == 16) return slots_launch_m<256, 16>(ctx, a, grid, smem);
     if (c.tpb == 128 && c.kt == 0)  return slots_launch_m<128, 0>(ctx, a, grid, smem);
     if (c.tpb == 128 && c.kt == 32) return slots_launch_t<128, -1, 32>(ctx, a, grid, smem);
-    if (c.tpb == 64) return slots_launch_t<64, -1, 0>(ctx, a, grid, smem);
-    return slots_launch_t<32, -1, 0>(ctx, a, grid, smem);
+    if (c.tpb == 64 && c.kt == 0)   return slots_launch_m<64, 0>(ctx, a, grid, smem);
+    if (c.tpb == 64 && c.kt == 32)  return slots_launch_t<64, -1, 32>(ctx, a, grid, smem);
+    return slots_launch_m<32, 0>(ctx, a, grid, smem);
 }
 #ifdef B2C_SLOT_TRACE
 extern "C" int b2c_debug_slot_trace(unsigned long long* out, int nwarps) {
@@ -1070,7 +1102,7 @@ static void emul_one(const MpcArgs& a, SlotMem& m, double* rec, int64_t i) {
             if (s.undo) { slot_undo<SS, KT>(a, m, true, s.undo == 2); s.undo = 0; }
             const bool gain = (s.mode == SLOT_FWD_GAIN), plain = !gain;
             double mv, lx, ly, lt;
-            const double Jn = slot_forward<SS, MT, KT>(a, m, s.z0x, s.z0y, s.z0t, s.alpha, true, gain, plain, mv, lx, ly, lt);
+            const double Jn = slot_forward<SS, MT, KT>(a, m, s.z0x, s.z0y, s.z0t, s.alpha, true, gain, plain, gain, mv, lx, ly, lt);
             slot_forward_post<SS, MT>(a, m, s, gain, Jn, mv, lx, ly, lt, 1);
         }
     }

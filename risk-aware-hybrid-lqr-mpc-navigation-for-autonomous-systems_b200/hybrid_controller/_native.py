@@ -235,3 +235,25 @@ def mpc_host(ctx, params, x0, xref, uref, obs, step_count=None, want_seq=True):
              _ptr(step_count), _ptr(out["u0"]), _ptr(out["cost"]), _ptr(out["status"]),
              _ptr(out["iters"]), _ptr(out["slack_used"]), _ptr(out["useq"]), _ptr(out["xpred"]))
     return out
+
+
+def mpc_table_host(ctx, params, table, k0, x0, obs, step_count=None, want_seq=True):
+    """Table form of solve_with_ltv (b2c_mpc_table_host): table (rows,6) = ReferenceTrajectoryGenerator.generate(),
+    k0 (B,) start rows, x0 (B,3), obs (B,M,3).  Instance i solves on get_trajectory_segment(k0[i], N+1) of the table;
+    results are bit-identical to mpc_host on the materialised segments."""
+    N, M = params.N, params.M
+    table = np.ascontiguousarray(table, dtype=np.float64).reshape(-1, 6)
+    x0 = _f64(x0).reshape(-1, 3)
+    B = x0.shape[0]
+    k0 = np.ascontiguousarray(np.broadcast_to(np.asarray(k0, np.int32), (B,)))
+    obs = _f64(obs, (B, M, 3)) if M else np.zeros((B, 0, 3))
+    if step_count is not None:
+        step_count = np.ascontiguousarray(step_count, dtype=np.int32).reshape(B).copy()
+    out = dict(u0=np.empty((B, 2)), cost=np.empty(B), status=np.empty(B, np.int32),
+               iters=np.empty(B, np.int32), slack_used=np.empty(B, np.int32),
+               useq=np.empty((B, N, 2)) if want_seq else None,
+               xpred=np.empty((B, N + 1, 3)) if want_seq else None, step_count=step_count)
+    ctx.call("b2c_mpc_table_host", B, C.byref(params), _ptr(table), int(table.shape[0]), _ptr(k0), _ptr(x0), _ptr(obs),
+             _ptr(step_count), _ptr(out["u0"]), _ptr(out["cost"]), _ptr(out["status"]),
+             _ptr(out["iters"]), _ptr(out["slack_used"]), _ptr(out["useq"]), _ptr(out["xpred"]))
+    return out

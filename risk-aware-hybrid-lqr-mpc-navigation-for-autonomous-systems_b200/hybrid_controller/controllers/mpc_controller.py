@@ -231,6 +231,20 @@ class MPCController:
         return self._batch(nat.MPC_LTI, x0, x_refs, u_refs, obstacles, None,
                            use_soft_constraints, want_seq)
 
+    def solve_with_ltv_table_batch(self, x0, table, k0, obstacles, step_count=None, want_seq: bool = True) -> Dict[str, Any]:
+        """solve_with_ltv for B instances that share one reference table: instance i solves on
+        ReferenceTrajectoryGenerator.get_trajectory_segment(k0[i], N+1) of `table` (rows,6), gathered on the device
+        (what run_simulation.py:247 does per robot before each call).  x0 (B,3), k0 (B,), obstacles (B,M,3) or (M,3).
+        Same outputs as solve_with_ltv_batch, bit-identical to it on the materialised segments."""
+        x0 = np.ascontiguousarray(x0, float).reshape(-1, 3)
+        B = x0.shape[0]
+        obstacles = np.asarray(obstacles, float)
+        if obstacles.ndim == 2:
+            obstacles = np.broadcast_to(obstacles[None], (B,) + obstacles.shape)
+        M = obstacles.shape[1] if obstacles.size else 0
+        prm = self._params(nat.MPC_LTV, M, soft=True)
+        return nat.mpc_table_host(self._ctx, prm, table, k0, x0, obstacles, step_count, want_seq=want_seq)
+
     def _batch(self, kind, x0, x_refs, u_refs, obstacles, step_count, soft, want_seq):
         x0 = np.ascontiguousarray(x0, float).reshape(-1, 3)
         B = x0.shape[0]

@@ -48,6 +48,31 @@ def mpc(params, x0, xref, uref, obs, step_count=None, slots=False):
                 step_count=sc)
 
 
+def mpc_slots_ex(params, x0, obs, xref=None, uref=None, table=None, k0=None, step_count=None):
+    """The slot state machine with the layouts the host entry points use: numpy instance-major inputs / outputs
+    (in_aos = out_aos = 1) and, with `table` + `k0`, the table form (segments gathered from the shared table)."""
+    from hybrid_controller import _native as nat
+    N, M = params.N, params.M
+    x0 = np.ascontiguousarray(np.asarray(x0, float).reshape(-1, 3))
+    B = x0.shape[0]
+    obs = np.ascontiguousarray(np.asarray(obs, float).reshape(B, -1)) if M else np.zeros((B, 1))
+    xr = None if xref is None else np.ascontiguousarray(np.asarray(xref, float).reshape(B, -1))
+    ur = None if uref is None else np.ascontiguousarray(np.asarray(uref, float).reshape(B, -1))
+    tab = None if table is None else np.ascontiguousarray(table, float)
+    kk = None if k0 is None else np.ascontiguousarray(k0, np.int32)
+    sc = None if step_count is None else np.ascontiguousarray(step_count, np.int32).copy()
+    u0, cost = np.empty((B, 2)), np.empty(B)
+    st, it, sl = (np.empty(B, np.int32) for _ in range(3))
+    useq, xpred = np.empty((B, N, 2)), np.empty((B, N + 1, 3))
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    f = lib().b2c_emul_mpc_slots_ex
+    f.argtypes = [C.c_int64, C.POINTER(nat.MpcParams), C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 12
+    rc = f(B, C.byref(params), 1, 1, p(tab), 0 if tab is None else tab.shape[0], p(kk), p(x0), p(xr), p(ur), p(obs),
+           p(sc), p(u0), p(cost), p(st), p(it), p(sl), p(useq), p(xpred))
+    assert rc == 0, rc
+    return dict(u0=u0, cost=cost, status=st, iters=it, slack_used=sl, useq=useq, xpred=xpred, step_count=sc)
+
+
 def dare(v, th, dt, Qd, Rd, method=1, guard=1):
     v, th = np.ascontiguousarray(v, float).ravel(), np.ascontiguousarray(th, float).ravel()
     B = v.size

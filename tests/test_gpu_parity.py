@@ -546,3 +546,93 @@ def test_mpc_slot_kernel_helper_lanes_follow_the_sequential_line_search(hc, N, M
     again = mpc.solve_with_ltv_batch(x0, xr, ur, ob)             # helpers or not, a relaunch reproduces every bit
     for key in ("u0", "cost", "iters", "useq", "xpred", "slack_used"):
         assert np.array_equal(out[key], again[key]), key
+
+
+# ------------------------------------------------------------------------------------------ round 2: table form, async, slot configs
+def _table_batch(B, N, M, seed):
+    from hybrid_controller import workloads as wl
+    table = wl.figure8_table()
+    rng = np.random.default_rng(seed)
+    k0 = rng.integers(0, 1000, B).astype(np.int32)
+    k0[:8] = [999, 998, 990, 985, 980, 979, 0, 1]                     # segments clamped at the last table row
+    idx = np.minimum(k0[:, None] + np.arange(N + 1)[None], len(table) - 1)
+    xr, ur = table[idx][:, :, 1:4].copy(), table[idx][:, :N, 4:6].copy()
+    x0 = xr[:, 0] + rng.uniform(-1, 1, (B, 3)) * [.1, .1, .2]
+    ob = np.broadcast_to(wl.DENSE_OBSTACLES[:M][None], (B, M, 3)).copy()
+    ob[:, :, :2] += rng.uniform(-.2, .2, (B, M, 2))
+    return table, k0, x0, xr, ur, ob
+
+
+@pytest.mark.parametrize("N,M,bs,B", [(20, 5, 1, 70000), (6, 3, 1, 3000), (6, 3, 2, 900), (20, 5, 1, 33)])
+def test_mpc_table_form_equals_materialised_segments(hc, N, M, bs, B):
+    """b2c_mpc_table_host (segments gathered on the device from the shared table, get_trajectory_segment's clamp,
+    HC/trajectory/reference_generator.py:299-326) == b2c_mpc_host on the materialised segments, every bit -- through
+    the slot path (chunked for the large batch) and, with move blocking, through the general kernel."""
+    from hybrid_controller.controllers.mpc_controller import MPCController
+    from hybrid_controller import workloads as wl
+    table, k0, x0, xr, ur, ob = _table_batch(B, N, M, seed=N + B)
+    x0[B // 2, 0] = np.nan
+    sc = (np.arange(B) % 12).astype(np.int32)
+    mpc = MPCController(horizon=N, block_size=bs, **wl.SIM_MPC)
+    a = mpc.solve_with_ltv_batch(x0, xr, ur, ob, step_count=sc)
+    b = mpc.solve_with_ltv_table_batch(x0, table, k0, ob, step_count=sc)
+    assert (a["status"] != 0).sum() == 1 and a["status"][B // 2] != 0
+    for k in ("u0", "cost", "status", "iters", "slack_used", "useq", "xpred", "step_count"):
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
+    c = mpc.solve_with_ltv_table_batch(x0, table, k0, ob, step_count=sc, want_seq=False)
+    assert np.array_equal(c["u0"], a["u0"], equal_nan=True) and c["useq"] is None
+
+
+def test_mpc_host_async_two_calls_in_flight(hc):
+    """b2c_mpc_host_async / b2c_mpc_table_host_async + b2c_wait: three calls issued back to back (the third waits for
+    the first's staging arena) give the results of the synchronous calls."""
+    import ctypes as C
+    from hybrid_controller import _native as nat
+    N, M, B = 20, 5, 20000
+    ctx = nat.Context(0)
+    prm = nat.mpc_params(nat.MPC_LTV, N, M, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02)
+    sets, outs = [], []
+    for s in range(3):
+        table, k0, x0, xr, ur, ob = _table_batch(B, N, M, seed=50 + s)
+        sets.append((table, k0, x0, xr, ur, ob))
+        outs.append(dict(u0=np.full((B, 2), np.nan), cost=np.full(B, np.nan), st=np.full(B, -1, np.int32),
+                         it=np.full(B, -1, np.int32), sl=np.full(B, -1, np.int32), useq=np.full((B, N, 2), np.nan)))
+    P = nat._ptr
+    for s, ((table, k0, x0, xr, ur, ob), o) in enumerate(zip(sets, outs)):
+        if s == 1:
+            ctx.call("b2c_mpc_table_host_async", B, C.byref(prm), P(table), table.shape[0], P(k0), P(x0), P(ob), None,
+                     P(o["u0"]), P(o["cost"]), P(o["st"]), P(o["it"]), P(o["sl"]), P(o["useq"]), None)
+        else:
+            ctx.call("b2c_mpc_host_async", B, C.byref(prm), P(x0), P(xr), P(ur), P(ob), None,
+                     P(o["u0"]), P(o["cost"]), P(o["st"]), P(o["it"]), P(o["sl"]), P(o["useq"]), None)
+    ctx.call("b2c_wait")
+    for (table, k0, x0, xr, ur, ob), o in zip(sets, outs):
+        ref = nat.mpc_host(ctx, prm, x0, xr, ur, ob)
+        assert (o["st"] == 0).all()
+        assert np.array_equal(o["u0"], ref["u0"]) and np.array_equal(o["cost"], ref["cost"])
+        assert np.array_equal(o["useq"], ref["useq"]) and np.array_equal(o["it"], ref["iters"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("N,M,B", [(20, 5, 50000), (20, 5, 3000), (6, 3, 9000)])
+def test_mpc_slot_configurations_agree_bit_for_bit(hc, N, M, B, monkeypatch):
+    """The slot kernel's configurations -- 256 slots per SM with the first 16 stages of the U strips in tensor memory
+    (tcgen05.ld / tcgen05.st), 128 slots per SM with everything in shared memory, 256 in shared memory for short
+    horizons -- run the same per-lane code on different storage: identical results, bit for bit."""
+    from hybrid_controller.controllers.mpc_controller import MPCController
+    from hybrid_controller import workloads as wl
+    x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=N + M + B, obstacles=wl.DENSE_OBSTACLES[:M],
+                                          pos_jitter=0.25, th_jitter=0.5, obs_jitter=0.25)
+    mpc = MPCController(horizon=N, block_size=1, **wl.SIM_MPC)
+    mpc.engine = 2
+    res = {}
+    cfgs = ["256,16", "128,0", "128,32", "64,0"] + (["256,0"] if N <= 6 else [])
+    for cfg in cfgs:
+        monkeypatch.setenv("B2C_SLOTS_CFG", cfg)
+        res[cfg] = mpc.solve_with_ltv_batch(x0, xr, ur, ob)
+    monkeypatch.delenv("B2C_SLOTS_CFG")
+    ref = res[cfgs[0]]
+    assert (ref["status"] == 0).all() and ref["iters"].max() >= 5
+    for cfg in cfgs[1:]:
+        for k in ("u0", "cost", "iters", "slack_used", "useq", "xpred"):
+            assert np.array_equal(ref[k], res[cfg][k]), (cfg, k)

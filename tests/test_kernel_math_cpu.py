@@ -127,6 +127,35 @@ def test_emul_slot_rejected_trials_are_undone():
     assert (np.abs(a["cost"] - b["cost"]) <= 1e-12 * np.abs(a["cost"])).all()
 
 
+def test_emul_slot_layouts_and_table_form_are_bit_identical():
+    """The slot path reads its inputs in three forms -- instance-minor SoA (b2c_mpc_dev), numpy instance-major
+    (the *_host entry points hand their staging buffers over as they are) and shared table + start row
+    (b2c_mpc_table_*: get_trajectory_segment on the device, HC/trajectory/reference_generator.py:299-326, clamped at
+    the end of the table) -- and must produce the same bits from each, incl. start rows whose segment runs off the table."""
+    from hybrid_controller import workloads as wl
+    table = wl.figure8_table()
+    rng = np.random.default_rng(3)
+    B, N, M = 600, 20, 5
+    k0 = rng.integers(0, 1000, B).astype(np.int32)
+    k0[:8] = [999, 998, 990, 985, 980, 979, 0, 1]                     # segments clamped at the last row
+    idx = np.minimum(k0[:, None] + np.arange(N + 1)[None], len(table) - 1)
+    xr, ur = table[idx][:, :, 1:4].copy(), table[idx][:, :N, 4:6].copy()
+    x0 = xr[:, 0] + rng.uniform(-1, 1, (B, 3)) * [.1, .1, .2]
+    x0[5, 2] += 2 * np.pi                                              # another 2 pi branch
+    x0[17, 1] = np.nan                                                 # fallback instance
+    ob = np.broadcast_to(wl.DENSE_OBSTACLES[None], (B, M, 3)).copy()
+    ob[:, :, :2] += rng.uniform(-.2, .2, (B, M, 2))
+    sc = (np.arange(B) % 12).astype(np.int32)
+    p = _params(N, M, 1)
+    soa = emul.mpc(p, x0, xr, ur, ob, step_count=sc, slots=True)
+    aos = emul.mpc_slots_ex(p, x0, ob, xref=xr, uref=ur, step_count=sc)
+    tab = emul.mpc_slots_ex(p, x0, ob, table=table, k0=k0, step_count=sc)
+    assert soa["status"][17] != 0 and (soa["status"] != 0).sum() == 1 and soa["slack_used"].sum() > 0
+    for k in ("u0", "cost", "status", "iters", "slack_used", "useq", "xpred", "step_count"):
+        assert np.array_equal(soa[k], aos[k], equal_nan=True), k
+        assert np.array_equal(soa[k], tab[k], equal_nan=True), k
+
+
 def test_emul_mpc_g_mpc_golden(golden):
     g = golden["g_mpc"]
     traj = lin_dare.figure8(20.0)

@@ -38,7 +38,7 @@ def main():
         ctx.call("b2c_mpc_dev", B, C.byref(prm), d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), d[3].data_ptr(),
                  None, u0.data_ptr(), cost.data_ptr(), st.data_ptr(), it.data_ptr(), sl.data_ptr(), None, None)
         ctx.sync()
-    nw = min(4096, 148 * 4)
+    nw = min(8192, 148 * 8)
     buf = (C.c_ulonglong * (16 * nw))()
     f = ctx.lib.b2c_debug_slot_trace
     f.argtypes = [C.c_void_p, C.c_int]
@@ -59,8 +59,7 @@ def main():
         "cycles_per_round": {"backward": float(cyc[:, 0].sum() / rounds.sum()),
                              "refill": float(cyc[:, 1].sum() / rounds.sum()),
                              "forward": float(cyc[:, 2].sum() / rounds.sum())},
-        "refill_cycles_per_round": dict(zip(("claim", "rows_in_flight", "unwrap", "sincos_stage", "rows_issued_at", "owner_done_at"),
-                                            (t[:, 8:14].sum(axis=0) / rounds.sum()).tolist())),
+        "slots_cfg": os.environ.get("B2C_SLOTS_CFG", "auto"),
         "us_per_round_mean": float(((t[:, 1] - t[:, 0]) / 1e3).sum() / rounds.sum()),
     }))
 
