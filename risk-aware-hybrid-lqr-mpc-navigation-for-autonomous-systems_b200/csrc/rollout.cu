@@ -9,12 +9,14 @@
 //   DifferentialDriveRobot.simulate_step             HC/models/differential_drive.py:138-172 (clip, Euler, wrap)
 //
 // Per tick:  k_roll_decide (every robot: reference row, risk, hysteresis; LQR robots get their control from the
-// per-row gain table, MPC robots are appended to a work list)  ->  k_roll_gather (work list -> SoA QP inputs)
-// ->  b2c_mpc_dev (the K3 kernels, unchanged)  ->  k_roll_scatter  ->  k_roll_plant (every robot).
+// per-row gain table, MPC robots are appended to a work list)  ->  k_roll_gather (work list -> state, obstacles,
+// start row of the QP: the table form of K3 gathers the reference segment itself)  ->  the K3 kernels, unchanged,
+// which read the length of the work list FROM DEVICE MEMORY  ->  k_roll_scatter  ->  k_roll_plant (every robot).
+// Nothing in the loop waits for the host: a 500-tick rollout is 500 x 7 launches enqueued back to back.
 // The LQR gain depends on the table row only (compute_gain(u_ref[0], x_ref[2]), lqr_controller.py:191-215), so
 // the DARE runs once per table row per call (K2), not once per robot per tick.
 #include <vector>
-#include "b2c_common.cuh"
+#include "mpc_args.cuh"
 
 namespace {
 
@@ -132,17 +134,13 @@ B2C_HD void roll_plant_one(const RollArgs& g, int64_t r) {
     if (hit) g.counters[3 * R + r] += 1;
 }
 
-// QP inputs of work item j (robot r): x0 = state, reference rows k..k+N from the table, the robot's obstacles
-B2C_HD void roll_gather_one(const RollArgs& g, int64_t j, int64_t cap, double* x0, double* xref, double* uref,
+// QP inputs of work item j (robot r): x0 = state, first reference row (the table form of K3 takes rows k..k+N of
+// the shared table itself, clamped at its end like get_trajectory_segment), the robot's obstacles
+B2C_HD void roll_gather_one(const RollArgs& g, int64_t j, int64_t cap, double* x0, int32_t* qk0,
                             double* ob, int32_t* sc, const int32_t* step_count) {
     const int64_t r = g.work[j], R = g.R;
     x0[j] = g.x[r]; x0[cap + j] = g.x[R + r]; x0[2 * cap + j] = g.x[2 * R + r];
-    for (int k = 0; k <= g.N; ++k) {
-        const double* row = g.table + (int64_t)roll_row(g, r, k) * 6;
-        xref[(int64_t)(3 * k) * cap + j] = row[1]; xref[(int64_t)(3 * k + 1) * cap + j] = row[2];
-        xref[(int64_t)(3 * k + 2) * cap + j] = row[3];
-        if (k < g.N) { uref[(int64_t)(2 * k) * cap + j] = row[4]; uref[(int64_t)(2 * k + 1) * cap + j] = row[5]; }
-    }
+    qk0[j] = roll_row(g, r, 0);
     for (int e = 0; e < 3 * g.M; ++e) ob[(int64_t)e * cap + j] = g.obs[(int64_t)e * R + r];
     sc[j] = step_count[r];
 }
@@ -171,17 +169,17 @@ __global__ void __launch_bounds__(256) k_roll_plant(const RollArgs g) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r < g.R) roll_plant_one(g, r);
 }
+// the work list's length is read on the device (no host round trip per tick); the grid covers all R robots
 __global__ void __launch_bounds__(256)
-k_roll_gather(const RollArgs g, int64_t n, int64_t cap, double* x0, double* xref, double* uref, double* ob,
-              int32_t* sc, const int32_t* step_count) {
+k_roll_gather(const RollArgs g, int64_t cap, double* x0, int32_t* qk0, double* ob, int32_t* sc, const int32_t* step_count) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < n) roll_gather_one(g, j, cap, x0, xref, uref, ob, sc, step_count);
+    if (j < (int64_t)*g.nwork) roll_gather_one(g, j, cap, x0, qk0, ob, sc, step_count);
 }
 __global__ void __launch_bounds__(256)
-k_roll_scatter(const RollArgs g, int64_t n, int64_t cap, const double* u0, const int32_t* sc, const int32_t* st,
+k_roll_scatter(const RollArgs g, int64_t cap, const double* u0, const int32_t* sc, const int32_t* st,
                int32_t* step_count) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < n) roll_scatter_one(g, j, cap, u0, sc, st, step_count);
+    if (j < (int64_t)*g.nwork) roll_scatter_one(g, j, cap, u0, sc, st, step_count);
 }
 // (the work list is filled with atomics, so its order varies from launch to launch; nothing a robot computes
 // depends on its position in the list)
@@ -237,13 +235,13 @@ int b2c_rollout_dev(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const 
     if (g.M > 0 && !obs) { b2c_set_error("obstacles missing"); return -1; }
     B2C_DEVICE_GUARD(ctx);
     const bool qp = p->mode != B2C_ROLL_LQR;
-    const int N = g.N, M = g.M, rows = g.rows;
-    // ---- working memory (context-owned, second arena so that the K3 scratch stays untouched) ---------------
+    const int M = g.M, rows = g.rows;
+    // ---- working memory (context-owned arena, apart from the K3 scratch) ------------------------------------
     size_t need = al256(6 * rows * 8) + 2 * al256(rows * 8) + 2 * al256(rows * 4)     // gain table, v/th columns
                 + al256(2 * R * 8) + 2 * al256(R * 4) + al256(R * 4) + 256              // u, prev, since, work, nwork
                 + al256(R * 4);                                                         // step counters if not given
-    if (qp) need += al256(3 * R * 8) + al256(3 * (N + 1) * R * 8) + al256(2 * N * R * 8) + al256((3 * M + 1) * R * 8)
-                  + al256(2 * R * 8) + al256(R * 8) + 4 * al256(R * 4);
+    if (qp) need += al256(3 * R * 8) + al256(R * 4) + al256((3 * M + 1) * R * 8) + al256(2 * R * 8) + al256(R * 8)
+                  + 4 * al256(R * 4);
     rc = b2c_reserve(&ctx->dstage, &ctx->dstage_bytes, need, false);
     if (rc) return rc;
     char* base = (char*)ctx->dstage; size_t off = 0;
@@ -254,10 +252,10 @@ int b2c_rollout_dev(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const 
     g.u = (double*)take(2 * R * 8); g.prev = (int32_t*)take(R * 4); g.since = (int32_t*)take(R * 4);
     g.work = (int32_t*)take(R * 4); g.nwork = (unsigned long long*)take(256);
     int32_t* own_sc = (int32_t*)take(R * 4);
-    double *q_x0 = nullptr, *q_xr = nullptr, *q_ur = nullptr, *q_ob = nullptr, *q_u0 = nullptr, *q_cost = nullptr;
-    int32_t *q_sc = nullptr, *q_st = nullptr, *q_it = nullptr, *q_sl = nullptr;
+    double *q_x0 = nullptr, *q_ob = nullptr, *q_u0 = nullptr, *q_cost = nullptr;
+    int32_t *q_k0 = nullptr, *q_sc = nullptr, *q_st = nullptr, *q_it = nullptr, *q_sl = nullptr;
     if (qp) {
-        q_x0 = (double*)take(3 * R * 8); q_xr = (double*)take(3 * (N + 1) * R * 8); q_ur = (double*)take(2 * N * R * 8);
+        q_x0 = (double*)take(3 * R * 8); q_k0 = (int32_t*)take(R * 4);
         q_ob = (double*)take((3 * M + 1) * R * 8); q_u0 = (double*)take(2 * R * 8); q_cost = (double*)take(R * 8);
         q_sc = (int32_t*)take(R * 4); q_st = (int32_t*)take(R * 4); q_it = (int32_t*)take(R * 4); q_sl = (int32_t*)take(R * 4);
     }
@@ -278,34 +276,30 @@ int b2c_rollout_dev(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const 
     }
     k_roll_init<<<b2c_blocks(R, 256), 256, 0, s>>>(g);
     B2C_CHECK_LAUNCH(ctx);
-    unsigned long long* h_n = nullptr;
-    B2C_CUDA(cudaMallocHost((void**)&h_n, sizeof(unsigned long long)));
-    b2c_mpc_params mp = p->mpc;
+    const int rblocks = b2c_blocks(R, 256);
     for (int t = 0; t < p->ticks; ++t) {
         g.t = t;
         const bool may_solve = qp && !(p->mode == B2C_ROLL_MPC && (t % g.mpc_rate) != 0);
         if (may_solve) B2C_CUDA(cudaMemsetAsync(g.nwork, 0, sizeof(unsigned long long), s));
-        k_roll_decide<<<b2c_blocks(R, 256), 256, 0, s>>>(g);
+        k_roll_decide<<<rblocks, 256, 0, s>>>(g);
         B2C_CHECK_LAUNCH(ctx);
         if (may_solve) {
-            B2C_CUDA(cudaMemcpyAsync(h_n, g.nwork, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-            B2C_CUDA(cudaStreamSynchronize(s));
-            const int64_t n = (int64_t)*h_n;
-            if (n > 0) {
-                k_roll_gather<<<b2c_blocks(n, 256), 256, 0, s>>>(g, n, n, q_x0, q_xr, q_ur, q_ob, q_sc, step_count);
-                B2C_CHECK_LAUNCH(ctx);
-                rc = b2c_mpc_dev(ctx, n, &mp, q_x0, q_xr, q_ur, q_ob, q_sc, q_u0, q_cost, q_st, q_it, q_sl, nullptr, nullptr);
-                if (rc) { cudaFreeHost(h_n); return rc; }
-                k_roll_scatter<<<b2c_blocks(n, 256), 256, 0, s>>>(g, n, n, q_u0, q_sc, q_st, step_count);
-                B2C_CHECK_LAUNCH(ctx);
-            }
+            // the QP batch of this tick: R is the capacity (and the SoA stride), *g.nwork the number of instances
+            k_roll_gather<<<rblocks, 256, 0, s>>>(g, R, q_x0, q_k0, q_ob, q_sc, step_count);
+            B2C_CHECK_LAUNCH(ctx);
+            MpcArgs a;
+            mpc_fill_args(a, R, &p->mpc, q_x0, nullptr, nullptr, q_ob, q_sc, q_u0, q_cost, q_st, q_it, q_sl, nullptr, nullptr);
+            a.n_dev = g.nwork;
+            a.table = table; a.table_rows = rows; a.k0 = q_k0;
+            rc = mpc_table_launch(ctx, a, p->mpc.engine);
+            if (rc) return rc;
+            k_roll_scatter<<<rblocks, 256, 0, s>>>(g, R, q_u0, q_sc, q_st, step_count);
+            B2C_CHECK_LAUNCH(ctx);
         }
-        k_roll_plant<<<b2c_blocks(R, 256), 256, 0, s>>>(g);
+        k_roll_plant<<<rblocks, 256, 0, s>>>(g);
         B2C_CHECK_LAUNCH(ctx);
     }
-    cudaError_t e = cudaStreamSynchronize(s);
-    cudaFreeHost(h_n);
-    if (e != cudaSuccess) return b2c_cuda_fail(e, "rollout", __FILE__, __LINE__);
+    B2C_CUDA(cudaStreamSynchronize(s));
     return 0;
 }
 
@@ -324,8 +318,9 @@ int b2c_rollout_host(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const
                  b_lc = log_ctrl ? (size_t)T * R : 0;
     const size_t total = al256(b_tab) + al256(b_k0) + al256(b_x) + al256(b_obs) + al256(b_sc) + al256(b_cnt) +
                          al256(b_st) + al256(b_lx) + al256(b_lu) + al256(b_lr) + al256(b_lc) + 256;
-    char* d = nullptr;
-    B2C_CUDA(cudaMalloc((void**)&d, total));
+    int rc = b2c_reserve(&ctx->aux2, &ctx->aux2_bytes, total, false);       // context-owned: no cudaMalloc per call
+    if (rc) return rc;
+    char* d = (char*)ctx->aux2;
     size_t off = 0;
     auto take = [&](size_t bytes) { char* q = d + off; off += al256(bytes); return q; };
     double* d_tab = (double*)take(b_tab); int32_t* d_k0 = (int32_t*)take(b_k0); double* d_x = (double*)take(b_x);
@@ -334,7 +329,6 @@ int b2c_rollout_host(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const
     double* d_lx = log_x ? (double*)take(b_lx) : nullptr; double* d_lu = log_u ? (double*)take(b_lu) : nullptr;
     double* d_lr = log_risk ? (double*)take(b_lr) : nullptr; int8_t* d_lc = log_ctrl ? (int8_t*)take(b_lc) : nullptr;
     cudaStream_t s = ctx->stream;
-    int rc = 0;
     cudaError_t e = cudaSuccess;
     auto H2D = [&](void* dst, const void* src, size_t n) { if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s); };
     auto D2H = [&](void* dst, const void* src, size_t n) { if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, s); };
@@ -348,11 +342,11 @@ int b2c_rollout_host(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const
         D2H(x, d_x, b_x); D2H(counters, d_cnt, b_cnt); D2H(stats, d_st, b_st);
         if (mpc_step_count) D2H(mpc_step_count, d_sc, b_sc);
         D2H(log_x, d_lx, b_lx); D2H(log_u, d_lu, b_lu); D2H(log_risk, d_lr, b_lr); D2H(log_ctrl, d_lc, b_lc);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     }
-    cudaFree(d);
+    const cudaError_t e2 = cudaStreamSynchronize(s);  // nothing targets the caller's buffers after the return
     if (rc) return rc;
     if (e != cudaSuccess) return b2c_cuda_fail(e, "rollout host copies", __FILE__, __LINE__);
+    if (e2 != cudaSuccess) return b2c_cuda_fail(e2, "rollout", __FILE__, __LINE__);
     return 0;
 }
 #else
@@ -391,14 +385,21 @@ extern "C" int b2c_emul_rollout(int64_t R, const b2c_rollout_params* p, const do
         if (hit) counters[3 * R + r] = 1;
     }
     std::vector<double> q_x0(3 * R), q_xr(3 * (N + 1) * R), q_ur(2 * N * R + 1), q_ob(3 * M * R + 1), q_u0(2 * R), q_cost(R);
-    std::vector<int32_t> q_sc(R), q_st(R), q_it(R), q_sl(R);
+    std::vector<int32_t> q_sc(R), q_st(R), q_it(R), q_sl(R), q_k0(R);
     for (int t = 0; t < p->ticks; ++t) {
         g.t = t;
         int64_t n = 0;
         for (int64_t r = 0; r < R; ++r) if (roll_decide_one(g, r)) work[n++] = (int32_t)r;
         if (n > 0) {
-            for (int64_t j = 0; j < n; ++j)
-                roll_gather_one(g, j, n, q_x0.data(), q_xr.data(), q_ur.data(), q_ob.data(), q_sc.data(), step_count);
+            for (int64_t j = 0; j < n; ++j) {
+                roll_gather_one(g, j, n, q_x0.data(), q_k0.data(), q_ob.data(), q_sc.data(), step_count);
+                for (int k = 0; k <= N; ++k) {            // get_trajectory_segment(row, N+1), clamped at the end of the table
+                    const int rr = q_k0[j] + k < rows - 1 ? q_k0[j] + k : rows - 1;
+                    const double* row = table + (int64_t)rr * 6;
+                    q_xr[(3 * k) * n + j] = row[1]; q_xr[(3 * k + 1) * n + j] = row[2]; q_xr[(3 * k + 2) * n + j] = row[3];
+                    if (k < N) { q_ur[(2 * k) * n + j] = row[4]; q_ur[(2 * k + 1) * n + j] = row[5]; }
+                }
+            }
             b2c_emul_mpc(n, &p->mpc, q_x0.data(), q_xr.data(), q_ur.data(), q_ob.data(), q_sc.data(), q_u0.data(),
                          q_cost.data(), q_st.data(), q_it.data(), q_sl.data(), nullptr, nullptr);
             for (int64_t j = 0; j < n; ++j) roll_scatter_one(g, j, n, q_u0.data(), q_sc.data(), q_st.data(), step_count);
