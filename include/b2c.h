@@ -251,6 +251,19 @@ int b2c_rollout_host(b2c_ctx*, int64_t R, const b2c_rollout_params* p, const dou
                      int32_t* counters, double* stats,
                      double* log_x, double* log_u, double* log_risk, int8_t* log_ctrl);
 
+/* Synthetic robots of BASELINE config 5 (Monte-Carlo closed-loop rollouts), generated on the device from a
+ * counter-based stream keyed by (seed, GLOBAL robot index first_index + r): a robot is the same whatever the world size
+ * or shard, and a shard needs no host->device copy.  Per robot: start row k0 ~ U{0..k0_max-1}; state = table row k0
+ * [px,py,th] + U(+-pos_jitter, +-pos_jitter, +-th_jitter); obstacle m = base_obstacles[m] (HOST pointer, (M,3) [x,y,r],
+ * M <= 8) with centre shifted by U(+-obs_jitter)^2.  Outputs in the layouts b2c_rollout_dev takes: k0[R], x[3][R],
+ * obs[3M][R] (device pointers).  No counterpart in the reference (its runs are single-robot); the numpy mirror used by
+ * the tests is hybrid_controller/workloads.config5_robots.                                                           */
+int b2c_rollout_generate_dev(b2c_ctx*, int64_t R, int64_t first_index, uint64_t seed,
+                             const double* table, int32_t table_rows, int32_t k0_max,
+                             const double* base_obstacles, int32_t M,
+                             double pos_jitter, double th_jitter, double obs_jitter,
+                             int32_t* k0, double* x, double* obs);
+
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* register-resident FMA microbenchmark: returns achieved TFLOP/s (2 flop per FMA) for fp64
  * (bits=64) or fp32 (bits=32); used for the FP64 roofline denominator MEASURED_PEAKS lacks.   */

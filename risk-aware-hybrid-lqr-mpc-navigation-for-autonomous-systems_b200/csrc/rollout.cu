@@ -17,6 +17,7 @@
 // the DARE runs once per table row per call (K2), not once per robot per tick.
 #include <vector>
 #include "mpc_args.cuh"
+#define B2C_GEN_MAX_OBS 8
 
 namespace {
 
@@ -347,6 +348,63 @@ int b2c_rollout_host(b2c_ctx* ctx, int64_t R, const b2c_rollout_params* p, const
     if (rc) return rc;
     if (e != cudaSuccess) return b2c_cuda_fail(e, "rollout host copies", __FILE__, __LINE__);
     if (e2 != cudaSuccess) return b2c_cuda_fail(e2, "rollout", __FILE__, __LINE__);
+    return 0;
+}
+
+// ---- synthetic robots of BASELINE config 5 / SURVEY 8(d), generated on the device --------------------------------
+// Counter-based stream keyed by (seed, GLOBAL robot index): robot i is the same robot whatever the world size or the
+// shard it lands in, and a 1,048,576-robot shard needs no host->device copy.  Draw j of robot i is splitmix64 of
+// (seed ^ i * GOLDEN) + (j + 1) * GOLDEN, top 53 bits -> [0, 1).  Draws: 0 start row, 1-3 state offsets, 4 + 2m, 5 + 2m
+// the shift of obstacle m.  hybrid_controller/workloads.config5_robots is the numpy mirror (bit-identical; tested).
+struct GenArgs {
+    int64_t R, first; unsigned long long seed;
+    const double* table; int rows, k0_max, M;
+    double pos_jitter, th_jitter, obs_jitter;
+    double base[3 * B2C_GEN_MAX_OBS];
+    int32_t* k0; double* x; double* obs;
+};
+__device__ __forceinline__ double gen_u01(unsigned long long state, int j) {
+    unsigned long long z = state + (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+__global__ void __launch_bounds__(256) k_roll_generate(const GenArgs g) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= g.R) return;
+    const unsigned long long state = g.seed ^ ((unsigned long long)(g.first + r) * 0x9E3779B97F4A7C15ull);
+    int k0 = (int)(gen_u01(state, 0) * (double)g.k0_max);
+    if (k0 > g.k0_max - 1) k0 = g.k0_max - 1;
+    g.k0[r] = k0;
+    const double* row = g.table + (int64_t)(k0 < g.rows - 1 ? k0 : g.rows - 1) * 6;
+    const double jit[3] = {g.pos_jitter, g.pos_jitter, g.th_jitter};
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        g.x[(int64_t)c * g.R + r] = row[1 + c] + B2C_MUL(2.0 * gen_u01(state, 1 + c) - 1.0, jit[c]);
+    for (int m = 0; m < g.M; ++m) {
+        g.obs[(int64_t)(3 * m) * g.R + r] = g.base[3 * m] + B2C_MUL(2.0 * gen_u01(state, 4 + 2 * m) - 1.0, g.obs_jitter);
+        g.obs[(int64_t)(3 * m + 1) * g.R + r] = g.base[3 * m + 1] + B2C_MUL(2.0 * gen_u01(state, 5 + 2 * m) - 1.0, g.obs_jitter);
+        g.obs[(int64_t)(3 * m + 2) * g.R + r] = g.base[3 * m + 2];
+    }
+}
+
+int b2c_rollout_generate_dev(b2c_ctx* ctx, int64_t R, int64_t first_index, uint64_t seed,
+                             const double* table, int32_t table_rows, int32_t k0_max,
+                             const double* base_obstacles, int32_t M,
+                             double pos_jitter, double th_jitter, double obs_jitter,
+                             int32_t* k0, double* x, double* obs) {
+    if (!ctx || !table || !k0 || !x || (M > 0 && (!base_obstacles || !obs))) { b2c_set_error("null argument"); return -1; }
+    if (M < 0 || M > B2C_GEN_MAX_OBS || table_rows < 1 || k0_max < 1) { b2c_set_error("bad generator sizes"); return -2; }
+    if (R <= 0) return 0;
+    B2C_DEVICE_GUARD(ctx);
+    GenArgs g;
+    g.R = R; g.first = first_index; g.seed = seed; g.table = table; g.rows = table_rows; g.k0_max = k0_max; g.M = M;
+    g.pos_jitter = pos_jitter; g.th_jitter = th_jitter; g.obs_jitter = obs_jitter;
+    for (int e = 0; e < 3 * B2C_GEN_MAX_OBS; ++e) g.base[e] = e < 3 * M ? base_obstacles[e] : 0.0;
+    g.k0 = k0; g.x = x; g.obs = obs;
+    k_roll_generate<<<b2c_blocks(R, 256), 256, 0, ctx->stream>>>(g);
+    B2C_CHECK_LAUNCH(ctx);
     return 0;
 }
 #else

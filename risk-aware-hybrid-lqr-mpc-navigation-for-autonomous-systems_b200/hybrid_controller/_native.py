@@ -84,6 +84,8 @@ SIGNATURES = {
     "b2c_mpc_static_max_instances": (C.c_int64, [C.POINTER(MpcParams)]),
     "b2c_rollout_dev": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
     "b2c_rollout_host": (C.c_int, [_P, C.c_int64, C.POINTER(RolloutParams)] + [_P] * 11),
+    "b2c_rollout_generate_dev": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_uint64, _P, C.c_int32, C.c_int32, _P, C.c_int32,
+                                           C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "b2c_measure_fma_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
 }
 
@@ -151,6 +153,12 @@ class Context:
 
     def sync(self):
         self.call("b2c_sync")
+
+    @property
+    def stream_handle(self):
+        """the cudaStream_t the context launches on, as an integer"""
+        self.lib.b2c_stream.restype = _P
+        return int(self.lib.b2c_stream(self.h) or 0)
 
     @property
     def launches(self):

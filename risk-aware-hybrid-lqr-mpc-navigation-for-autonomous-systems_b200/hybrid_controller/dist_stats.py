@@ -25,7 +25,19 @@ def solve_stats(status, iters, slack_used, cost=None):
     return s
 
 
-_MAX_KEYS = ("iters_max", "cost_max")
+def rollout_stats(out, ticks):
+    """Per-shard statistics of a closed-loop rollout (simulate_batch / simulate_generated_shard result) -> dict of
+    numpy scalars: the <= 1 KB vector that is all-reduced over the ranks at the end of a config-5 run."""
+    R = len(out["lqr_steps"])
+    return {"robots": np.int64(R), "robot_steps": np.int64(R) * np.int64(ticks),
+            "lqr_steps": np.int64(out["lqr_steps"].sum(dtype=np.int64)), "mpc_solves": np.int64(out["mpc_solves"].sum(dtype=np.int64)),
+            "switches": np.int64(out["switches"].sum(dtype=np.int64)),
+            "collision_states": np.int64(out["collision_states"].sum(dtype=np.int64)),
+            "mpc_fallbacks": np.int64(out["mpc_fallbacks"].sum(dtype=np.int64)),
+            "err_mean_sum": np.float64(out["mean_error"].sum()), "err_max": np.float64(out["max_error"].max())}
+
+
+_MAX_KEYS = ("iters_max", "cost_max", "err_max")
 
 
 def reduce_stats(stats, device=None):

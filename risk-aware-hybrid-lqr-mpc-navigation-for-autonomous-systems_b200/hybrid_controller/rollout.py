@@ -80,6 +80,51 @@ def simulate_batch(mode: str, table, k0, x0, obstacles, ticks: int, lqr=None, mp
     return out
 
 
+def simulate_generated_shard(R: int, first_index: int, seed: int, table, ticks: int, mode: str = "hybrid", lqr=None,
+                             mpc=None, risk=None, obstacles=None, k0_max: int = 500, pos_jitter: float = 0.1,
+                             th_jitter: float = 0.2, obs_jitter: float = 0.2, ctx=None, device=None, return_inputs: bool = False,
+                             **loop_kw) -> Dict[str, Any]:
+    """One shard of BASELINE config 5, entirely on the device: robots [first_index, first_index + R) are GENERATED there
+    (b2c_rollout_generate_dev: counter-based stream keyed by (seed, global robot index), so the shard split never
+    changes a robot) and rolled out by b2c_rollout_dev; only the per-robot counters / statistics come back.
+    Device memory comes from torch (imported here, not at package import).  Returns the simulate_batch dict without
+    logs, plus `elapsed_s` (CUDA events around generation + rollout on the context's stream)."""
+    import torch
+    from . import workloads as wl
+    dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+    ctx = ctx or nat.default_context(dev.index)
+    table = np.ascontiguousarray(table, np.float64)
+    base = np.ascontiguousarray(wl.DEFAULT_OBSTACLES if obstacles is None else obstacles, np.float64).reshape(-1, 3)
+    M = base.shape[0]
+    p = rollout_params(mode, ticks, table.shape[0], lqr, mpc, risk, M, **loop_kw)
+    d_tab = torch.from_numpy(table).to(dev)
+    d_k0 = torch.empty(R, dtype=torch.int32, device=dev)
+    d_x = torch.empty((3, R), dtype=torch.float64, device=dev)
+    d_ob = torch.empty((max(3 * M, 1), R), dtype=torch.float64, device=dev)
+    cnt = torch.empty((5, R), dtype=torch.int32, device=dev)
+    sts = torch.empty((3, R), dtype=torch.float64, device=dev)
+    torch.cuda.synchronize(dev)
+    stream = torch.cuda.ExternalStream(ctx.stream_handle, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    ctx.call("b2c_rollout_generate_dev", R, int(first_index), int(seed), d_tab.data_ptr(), table.shape[0], int(k0_max),
+             nat._ptr(base), M, float(pos_jitter), float(th_jitter), float(obs_jitter), d_k0.data_ptr(), d_x.data_ptr(),
+             d_ob.data_ptr())
+    inputs = (d_k0.cpu().numpy(), d_x.t().cpu().numpy().copy(), d_ob[:3 * M].t().cpu().numpy().reshape(R, M, 3).copy()) \
+        if return_inputs else None
+    ctx.call("b2c_rollout_dev", R, C.byref(p), d_tab.data_ptr(), d_k0.data_ptr(), d_x.data_ptr(), d_ob.data_ptr(), None,
+             cnt.data_ptr(), sts.data_ptr(), None, None, None, None)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    c, st = cnt.cpu().numpy(), sts.cpu().numpy()
+    out = dict(x=d_x.t().cpu().numpy().copy(), lqr_steps=c[0], mpc_solves=c[1], switches=c[2], collision_states=c[3],
+               mpc_fallbacks=c[4], mean_error=st[0] / max(ticks, 1), max_error=st[1], final_error=st[2],
+               elapsed_s=e0.elapsed_time(e1) * 1e-3)
+    if return_inputs:
+        out["inputs"] = inputs
+    return out
+
+
 def export_robot_csv(out: Dict[str, Any], r: int, table, k0: int, log_dir: str, stamp: str, mode: str = "hybrid",
                      wrap_error: Optional[bool] = None):
     """Write robot r of a simulate_batch(log=True) result in the reference's run-log schema

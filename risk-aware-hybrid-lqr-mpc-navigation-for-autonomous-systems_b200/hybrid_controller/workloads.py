@@ -65,6 +65,40 @@ def config4_instances(B, N=20, seed=0, start=0, count=None, obstacles=DENSE_OBST
     return x0, x_refs, u_refs, obs
 
 
+_GOLDEN = np.uint64(0x9E3779B97F4A7C15)
+
+
+def _u01(state, j):
+    """draw j of the counter-based stream (numpy mirror of gen_u01 in csrc/rollout.cu; uint64 arithmetic wraps)"""
+    with np.errstate(over="ignore"):
+        z = state + np.uint64(j + 1) * _GOLDEN
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def config5_robots(R, first_index=0, seed=0, table=None, k0_max=500, obstacles=DEFAULT_OBSTACLES,
+                   pos_jitter=0.1, th_jitter=0.2, obs_jitter=0.2):
+    """Robots [first_index, first_index + R) of BASELINE config 5, keyed by GLOBAL robot index: the numpy
+    mirror of b2c_rollout_generate_dev, bit-identical to it.  Returns k0 (R,) int32, x0 (R,3), obs (R,M,3)."""
+    table = figure8_table() if table is None else np.asarray(table, float)
+    obstacles = np.asarray(obstacles, float).reshape(-1, 3)
+    with np.errstate(over="ignore"):
+        state = np.uint64(seed) ^ ((np.arange(R, dtype=np.uint64) + np.uint64(first_index)) * _GOLDEN)
+    k0 = np.minimum((_u01(state, 0) * float(k0_max)).astype(np.int32), k0_max - 1)
+    rows = table[np.minimum(k0, len(table) - 1)]
+    jit = (pos_jitter, pos_jitter, th_jitter)
+    x0 = np.stack([rows[:, 1 + c] + (2.0 * _u01(state, 1 + c) - 1.0) * jit[c] for c in range(3)], axis=1)
+    M = len(obstacles)
+    obs = np.empty((R, M, 3))
+    for m in range(M):
+        obs[:, m, 0] = obstacles[m, 0] + (2.0 * _u01(state, 4 + 2 * m) - 1.0) * obs_jitter
+        obs[:, m, 1] = obstacles[m, 1] + (2.0 * _u01(state, 5 + 2 * m) - 1.0) * obs_jitter
+        obs[:, m, 2] = obstacles[m, 2]
+    return k0, x0, obs
+
+
 def shard_range(B, rank, world):
     """Contiguous block split of the global index range."""
     per = B // world
