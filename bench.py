@@ -2,12 +2,14 @@
 """Headline benchmark: MPC QP solves/sec (diff-drive, N=20, 5 obstacles) -- BASELINE.json config 4.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
-One process per GPU (torchrun for N>1); a "step" = one pass of the K3 kernel over one batch of
+One process per GPU (torchrun for N>1); a "step" = one pass of the K3 kernels over one batch of
 65,536 independent solve_with_ltv instances.  Weak scaling: every rank owns its own 65,536-instance
-shard of a global batch of N*65,536 (no data-path collective; one all-reduce(MAX) of the time).
+shard of a global batch of N*65,536 (no data-path collective; one all-reduce(MAX) of the time, and the
+<= 1 KB statistics vector of the config-5 leg over NCCL).
 Prints ONE JSON line on rank 0.  See DESIGN.md section 6 for how each field is obtained.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -27,12 +29,22 @@ B_PER_GPU = 65536
 HORIZON, N_OBS = 20, 5
 METRIC = "MPC QP solves/sec (diff-drive, N=20, 5 obstacles)"
 WORKLOAD = "config4: 65,536 independent solve_with_ltv instances per GPU, N=20, M=5 dense obstacles, block_size=1"
-# algorithmic bytes per solve: inputs 24+504+320+120 = 968 B, outputs u0+cost+status+iters = 32 B
-ALG_BYTES_PER_SOLVE = 1000.0
-# counted fp64 flops per stage (DESIGN.md section 5): backward Riccati stage / forward stage with 5 rows
+# algorithmic bytes per solve: inputs 24+504+320+120 = 968 B, outputs u0+cost+status+iters = 32 B;
+# with control_sequence + predicted_states written: + 320 + 504 = 1,824 B
+ALG_BYTES_PER_SOLVE, ALG_BYTES_FULL = 1000.0, 1824.0
+# counted fp64 flops per stage (DESIGN.md section 4): backward Riccati stage / forward stage with 5 rows
 FLOP_BWD_STAGE, FLOP_FWD_STAGE = 262.0, 215.0
 ORACLE_PRM = dict(N=HORIZON, Qd=[15, 15, 50], Rd=[.1, .1], Pd=[30, 30, 40], d_safe=.3, rho=5000., v_max=2.,
                   w_max=3., dt=.02, block_size=1)
+KERNEL_SRCS = ("mpc_slots.cu", "mpc_args.cuh", "b2c_common.cuh")
+
+
+def kernel_src_sha():
+    """hash of the sources of the dominant kernel: ties a committed ncu traffic figure to the code it was taken from"""
+    h = hashlib.sha256()
+    for f in KERNEL_SRCS:
+        h.update(open(os.path.join(PKG, "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 def _oracle_solve(args):
@@ -42,15 +54,25 @@ def _oracle_solve(args):
     return o["optimal_control"]
 
 
+def _oracle_gain(args):
+    from oracle import lin_dare
+    v, th = args
+    return lin_dare.lqr_gain(v, th, [15, 15, 8], [.1, .1], .02)[0]
+
+
 def cpu_arm(n_instances, seed, pool, global_batch=None):
-    """Time the CPU implementation of the path on `n_instances` config-4 instances (all host cores).
-    With `global_batch` the instances are the FIRST n of that seeded global batch (same as the GPU's)."""
+    """Time the CPU implementation of the path on `n_instances` config-4 instances (all host cores, or this
+    process alone when pool is None).  With `global_batch` the instances are the FIRST n of that seeded global
+    batch (same as the GPU's)."""
     from hybrid_controller import workloads as wl
     x0, xr, ur, ob = wl.config4_instances(global_batch or n_instances, N=HORIZON, seed=seed, start=0,
                                           count=n_instances)
     items = [(x0[i], xr[i], ur[i], ob[i]) for i in range(n_instances)]
     t0 = time.perf_counter()
-    res = pool.map(_oracle_solve, items, chunksize=max(1, n_instances // (4 * pool._processes)))
+    if pool is None:
+        res = [_oracle_solve(it) for it in items]
+    else:
+        res = pool.map(_oracle_solve, items, chunksize=max(1, n_instances // (4 * pool._processes)))
     dt = time.perf_counter() - t0
     return n_instances / dt, dt, np.array(res)
 
@@ -95,7 +117,8 @@ def run_reference(args):
             "config": {"workload": WORKLOAD, "sample_per_step": sample},
             "cpu_baseline": {"value": v, "unit": "solves/s", "cores": cores, "kind": "port",
                              "sample": f"{sample} config-4 instances per step x {args.steps} steps; oracle port "
-                                       "(HiGHS active-set + KKT polish), cvxpy absent from the image"},
+                                       "(HiGHS active-set + KKT polish), cvxpy absent from the image",
+                             "reference_shipped_log_ms_per_solve": 82.6},
             "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -131,43 +154,77 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-def secondary_metrics(ctx, dev, stream):
-    """SURVEY 8(d) secondary figures, device-resident, CUDA-event timed on the context's stream (N=1 only):
-    config 3 (2^20 DARE gains, 2^20 linearizations), batch=1 MPC latency at the run_simulation shape (config 2) and a
-    config-5 shard of the hybrid closed loop (65,536 robots x 100 ticks)."""
+def secondary_metrics(ctx, dev, stream, with_cpu):
+    """SURVEY 8(d) secondary figures (N=1 only), device-resident, CUDA-event timed on the context's stream: config 3
+    (2^20 DARE gains, 2^20 linearizations, each with its CPU baseline) and batch=1 MPC latency at the
+    run_simulation shape (config 2)."""
     import ctypes as C
     import torch
-    from hybrid_controller import _native as nat, workloads as wl, rollout as ro
-    from hybrid_controller.controllers import LQRController, MPCController, RiskMetrics
+    from hybrid_controller import _native as nat, workloads as wl
+    from hybrid_controller.controllers import MPCController
     out = {}
 
     def timed(fn, reps):
-        fn(); torch.cuda.synchronize()
+        fn(0); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for _ in range(reps):
-            fn()
+        for r in range(reps):
+            fn(r)
         e1.record(stream); torch.cuda.synchronize()
         return e0.elapsed_time(e1) * 1e-3 / reps
 
-    n = 1 << 20
+    n, R = 1 << 20, 8                                # R rotating input / output sets: 8 x 143 MB > the 126 MB L2
     v, th = wl.config3_points(n)
-    dv, dth = torch.from_numpy(v).to(dev), torch.from_numpy(th).to(dev)
-    Kd = torch.empty((6, n), dtype=torch.float64, device=dev)
-    Pd = torch.empty((6, n), dtype=torch.float64, device=dev)
+    dv = [torch.from_numpy(np.roll(v, 1000 * r)).to(dev) for r in range(R)]
+    dth = [torch.from_numpy(np.roll(th, 1000 * r)).to(dev) for r in range(R)]
+    Kd = [torch.empty((6, n), dtype=torch.float64, device=dev) for _ in range(R)]
+    Pd = [torch.empty((6, n), dtype=torch.float64, device=dev) for _ in range(R)]
     it = torch.empty(n, dtype=torch.int32, device=dev); st = torch.empty(n, dtype=torch.int32, device=dev)
     Q, Rr = (C.c_double * 3)(15., 15., 8.), (C.c_double * 2)(.1, .1)
-    t = timed(lambda: ctx.call("b2c_dare_dev", n, nat.LIN_EULER, nat.GUARD_LQR, 0.02, Q, Rr, dv.data_ptr(), dth.data_ptr(),
-                               Kd.data_ptr(), Pd.data_ptr(), it.data_ptr(), st.data_ptr()), 10)
-    flops = 520.0 * float(it.float().mean().item()) + 160.0
-    out["dare_config3"] = {"points": n, "gains_per_s": n / t, "ms": t * 1e3, "mean_doubling_steps": float(it.float().mean().item()),
+    t = timed(lambda r: ctx.call("b2c_dare_dev", n, nat.LIN_EULER, nat.GUARD_LQR, 0.02, Q, Rr, dv[r % R].data_ptr(),
+                                 dth[r % R].data_ptr(), Kd[r % R].data_ptr(), Pd[r % R].data_ptr(), it.data_ptr(),
+                                 st.data_ptr()), 16)
+    I = float(it.float().mean().item())
+    out["dare_config3"] = {"points": n, "gains_per_s": n / t, "ms": t * 1e3, "mean_doubling_steps": I,
                            "ok_frac": float((st == 0).float().mean().item()), "alg_bytes_per_point": 136,
-                           "hbm_gbs": 136 * n / t / 1e9, "fp64_tflops": flops * n / t / 1e12}
-    Ad = torch.empty((9, n), dtype=torch.float64, device=dev); Bd = torch.empty((6, n), dtype=torch.float64, device=dev)
-    t = timed(lambda: ctx.call("b2c_linearize_dev", n, nat.LIN_EULER, nat.GUARD_NONE, 0.02, dv.data_ptr(), dth.data_ptr(),
-                               Ad.data_ptr(), Bd.data_ptr()), 20)
+                           "hbm_gbs": 136 * n / t / 1e9,
+                           "fp64_tflops": (520.0 * I + 160.0) * n / t / 1e12,
+                           "fp64_tflops_baseline_md_formula": (420.0 * I + 160.0) * n / t / 1e12,
+                           "flop_formula": "520*I+160 counted from csrc/lin_dare.cu (eight general 3x3 products per doubling "
+                                           "step); BASELINE.md section 4 estimates 420*I+160 -- both reported"}
+    Ad = [torch.empty((9, n), dtype=torch.float64, device=dev) for _ in range(R)]
+    Bd = [torch.empty((6, n), dtype=torch.float64, device=dev) for _ in range(R)]
+    t = timed(lambda r: ctx.call("b2c_linearize_dev", n, nat.LIN_EULER, nat.GUARD_NONE, 0.02, dv[r % R].data_ptr(),
+                                 dth[r % R].data_ptr(), Ad[r % R].data_ptr(), Bd[r % R].data_ptr()), 32)
     out["linearize_config3"] = {"points": n, "points_per_s": n / t, "ms": t * 1e3, "alg_bytes_per_point": 136,
-                                "hbm_gbs": 136 * n / t / 1e9}
+                                "hbm_gbs": 136 * n / t / 1e9,
+                                "l2": f"inputs and outputs rotate over {R} distinct sets ({R}x{136 * n / 1e6:.0f} MB > 126 MB L2)"}
+    del Ad, Bd, Kd, Pd
+    if with_cpu:
+        # CPU baselines (SURVEY 8d): the reference's own arithmetic -- scipy.linalg.solve_discrete_are + the gain
+        # formula of lqr_controller.py:126-132 (oracle/lin_dare.lqr_gain), 4,096-point slice, 1 core and all cores;
+        # get_discrete_model_explicit (linearization.py:190-225) as a Python loop over 65,536 points, 1 core
+        from oracle import lin_dare
+        pts = list(zip(v[:4096].tolist(), th[:4096].tolist()))
+        t0 = time.perf_counter()
+        for a in pts[:1024]:
+            _oracle_gain(a)
+        one = 1024 / (time.perf_counter() - t0)
+        pool, cores = make_pool()
+        pool.map(_oracle_gain, pts[:cores * 4])
+        t0 = time.perf_counter()
+        pool.map(_oracle_gain, pts, chunksize=64)
+        allc = 4096 / (time.perf_counter() - t0)
+        pool.close()
+        out["dare_config3"]["cpu_baseline"] = {"gains_per_s_1_core": one, "gains_per_s_all_cores": allc, "cores": cores,
+                                               "kind": "reference arithmetic (scipy.linalg.solve_discrete_are)",
+                                               "sample": "1,024 points on 1 core; 4,096 points on all cores"}
+        t0 = time.perf_counter()
+        for a, b in zip(v[:65536].tolist(), th[:65536].tolist()):
+            lin_dare.discrete_explicit(a, b, 0.02)
+        out["linearize_config3"]["cpu_baseline"] = {"points_per_s_1_core": 65536 / (time.perf_counter() - t0), "cores": 1,
+                                                    "kind": "port of get_discrete_model_explicit, Python loop",
+                                                    "sample": "65,536 points"}
     # batch = 1 latency through the drop-in class (host numpy in/out, wall clock): run_simulation.py --mode mpc shape
     mpc = MPCController(horizon=6, block_size=2, **wl.SIM_MPC)
     table = wl.figure8_table()
@@ -185,35 +242,43 @@ def secondary_metrics(ctx, dev, stream):
     out["mpc_batch1_latency_ms"] = {"mean": float(lat.mean()), "p50": float(np.percentile(lat, 50)),
                                     "p99": float(np.percentile(lat, 99)), "solves": int(lat.size),
                                     "reference_shipped_log_mean_ms": 82.6}
-    # config-5 shard
-    R, T = 65536, 100
-    rng = np.random.default_rng(0)
-    k0 = rng.integers(0, 500, R).astype(np.int32)
-    x0 = table[k0, 1:4] + rng.uniform(-1, 1, (R, 3)) * np.array([.1, .1, .2])
-    ob = np.broadcast_to(wl.DEFAULT_OBSTACLES[None], (R, 3, 3)).copy()
-    ob[:, :, :2] += rng.uniform(-.2, .2, (R, 3, 2))
-    p = ro.rollout_params("hybrid", T, table.shape[0], LQRController(**wl.SIM_LQR),
-                          MPCController(horizon=6, block_size=1, **wl.SIM_MPC),
-                          RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2, threshold_medium=0.5), 3)
-    d_tab = torch.from_numpy(table).to(dev); d_k0 = torch.from_numpy(k0).to(dev)
-    d_ob = torch.from_numpy(np.ascontiguousarray(ob.reshape(R, 9).T)).to(dev)
-    x_init = torch.from_numpy(np.ascontiguousarray(x0.T)).to(dev)
-    cnt = torch.zeros((5, R), dtype=torch.int32, device=dev); sts = torch.zeros((3, R), dtype=torch.float64, device=dev)
-    best = 1e9
-    for _ in range(3):
-        d_x = x_init.clone(); torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        ctx.call("b2c_rollout_dev", R, C.byref(p), d_tab.data_ptr(), d_k0.data_ptr(), d_x.data_ptr(), d_ob.data_ptr(), None,
-                 cnt.data_ptr(), sts.data_ptr(), None, None, None, None)
-        torch.cuda.synchronize()
-        best = min(best, time.perf_counter() - t0)
-    c = cnt.sum(dim=1).cpu().numpy().astype(float)
-    out["hybrid_rollout_config5_shard"] = {"robots": R, "ticks": T, "robot_steps_per_s": R * T / best,
-                                           "mpc_solve_fraction": c[1] / (R * T), "switches_per_robot": c[2] / R,
-                                           "collision_state_fraction": c[3] / (R * (T + 1)),
-                                           "mean_tracking_error_m": float((sts[0] / T).mean().item()),
-                                           "note": "tools/bench_rollout.py runs the full 1,048,576 x 500 shard"}
     return out
+
+
+def config5_leg(ctx, dev, rank, world, robots, ticks):
+    """BASELINE config 5: Monte-Carlo hybrid LQR-MPC closed-loop rollouts, `robots` per GPU x `ticks` plant steps,
+    batch-sharded by global robot index (inputs generated on the device from (seed, global index)); the aggregates are
+    combined with the design's only collective, the <= 1 KB statistics all-reduce (NCCL when world > 1)."""
+    import torch
+    import torch.distributed as dist
+    from hybrid_controller import workloads as wl, dist_stats
+    from hybrid_controller.rollout import simulate_generated_shard
+    from hybrid_controller.controllers import LQRController, MPCController, RiskMetrics
+    kw = dict(lqr=LQRController(**wl.SIM_LQR), mpc=MPCController(horizon=6, block_size=1, **wl.SIM_MPC),
+              risk=RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2, threshold_medium=0.5),
+              ctx=ctx, device=dev.index)
+    table = wl.figure8_table()
+    simulate_generated_shard(min(robots, 65536), 0, 1, table, min(ticks, 20), **kw)       # warm-up (arenas, modules)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    out = simulate_generated_shard(robots, rank * robots, 0, table, ticks, **kw)
+    el = torch.tensor([out["elapsed_s"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(el, op=dist.ReduceOp.MAX)
+    st = dist_stats.reduce_stats(dist_stats.rollout_stats(out, ticks), device=dev)
+    elapsed = float(el.item())
+    steps = float(st["robot_steps"])
+    return {"workload": f"config5: {robots:,} robots per GPU x {ticks} ticks, hybrid loop (risk -> hysteresis -> LQR | MPC(N=6, "
+                        "block 1) -> Euler plant), default 3 obstacles jittered, inputs generated on the device",
+            "robots_global": int(st["robots"]), "ticks": ticks, "elapsed_s_max_over_ranks": elapsed,
+            "robot_steps_per_s": steps / elapsed, "mpc_solves_per_s": float(st["mpc_solves"]) / elapsed,
+            "mpc_solve_fraction": float(st["mpc_solves"]) / steps, "switches_per_robot": float(st["switches"]) / float(st["robots"]),
+            "collision_state_fraction": float(st["collision_states"]) / (float(st["robots"]) * (ticks + 1)),
+            "mpc_fallbacks": int(st["mpc_fallbacks"]),
+            "mean_tracking_error_m": float(st["err_mean_sum"]) / float(st["robots"]), "max_tracking_error_m": float(st["err_max"]),
+            "stats_reduce": "torch.distributed all_reduce(SUM) + all_reduce(MAX) over " + ("NCCL" if world > 1 else "one rank (no-op)"),
+            "scaling": "weak"}
 
 
 def run_gpu(args):
@@ -239,114 +304,153 @@ def run_gpu(args):
     ctx = nat.Context(local, stream=stream.cuda_stream)
     prm = nat.mpc_params(nat.MPC_LTV, N, M, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02,
                          engine=args.engine)
-    kernel_name = "k_mpc<true> (general, HBM scratch)" if args.engine == 1 else "k_mpc_slots (persistent, smem scratch)"
+    kernel_name = "k_mpc<true> (general, HBM scratch)" if args.engine == 1 else \
+        "k_mpc_slots (persistent; strips in shared memory" + (", U in tensor memory)" if B >= 4 * 148 * 256 else ")")
 
     # ---- inputs: this rank's shard of the global batch, R rotating distinct batches (> L2 in total)
     R = 4
     gB = B * world
-    host_sets, dev_sets = [], []
+    table = wl.figure8_table()
+    h_table = torch.from_numpy(np.ascontiguousarray(table)).pin_memory()
+    host_sets, dev_sets, tab_sets = [], [], []
     for r in range(R):
-        x0, xr, ur, ob = wl.config4_instances(gB, N=N, seed=100 + r, start=rank * B, count=B)
+        x0, xr, ur, ob, k0 = wl.config4_instances(gB, N=N, seed=100 + r, start=rank * B, count=B, return_k0=True)
         host = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in
                 (x0, xr.reshape(B, -1), ur.reshape(B, -1), ob.reshape(B, -1))]
         host_sets.append(host)
+        tab_sets.append(torch.from_numpy(np.ascontiguousarray(k0.astype(np.int32))).pin_memory())
         dev_sets.append([h.to(dev).t().contiguous() for h in host])      # SoA [F][B], resident in HBM
     u0 = torch.empty((2, B), dtype=torch.float64, device=dev)
     cost = torch.empty(B, dtype=torch.float64, device=dev)
     st = torch.empty(B, dtype=torch.int32, device=dev)
     it = torch.empty(B, dtype=torch.int32, device=dev)
     sl = torch.empty(B, dtype=torch.int32, device=dev)
+    useq = torch.empty((2 * N, B), dtype=torch.float64, device=dev)
+    xpred = torch.empty((3 * (N + 1), B), dtype=torch.float64, device=dev)
+    scnt = torch.full((B,), 10, dtype=torch.int32, device=dev)
 
-    def step_dev(s):
+    def step_dev(s, full=False):
         d = dev_sets[s % R]
         ctx.call("b2c_mpc_dev", B, C.byref(prm), d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(),
-                 d[3].data_ptr(), None, u0.data_ptr(), cost.data_ptr(), st.data_ptr(), it.data_ptr(),
-                 sl.data_ptr(), None, None)
+                 d[3].data_ptr(), scnt.data_ptr() if full else None, u0.data_ptr(), cost.data_ptr(), st.data_ptr(),
+                 it.data_ptr(), sl.data_ptr(), useq.data_ptr() if full else None, xpred.data_ptr() if full else None)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for s in range(W):
-        step_dev(s)
-    barrier()
+    def allmax(x):
+        if world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def timed_dev(full, steps):
+        for s in range(W):
+            step_dev(s, full)
+        barrier()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        l0 = ctx.launches
+        barrier()
+        t0 = time.perf_counter()
+        ev[0].record(stream)
+        for s in range(steps):
+            step_dev(s, full)
+            ev[s + 1].record(stream)
+        barrier()
+        wall = time.perf_counter() - t0
+        per = np.array([ev[s].elapsed_time(ev[s + 1]) for s in range(steps)])
+        return allmax(ev[0].elapsed_time(ev[steps])), per, ctx.launches - l0, wall
+
     sampler = ClockSampler(local)
     sampler.start()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
-    l0 = ctx.launches
-    barrier()
-    t_wall0 = time.perf_counter()
-    ev[0].record(stream)
-    for s in range(K):
-        step_dev(s)
-        ev[s + 1].record(stream)
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    launches = ctx.launches - l0
-    per_launch_ms = np.array([ev[s].elapsed_time(ev[s + 1]) for s in range(K)])
-    total_ms = ev[0].elapsed_time(ev[K])
+    total_ms, per_launch_ms, launches, t_wall = timed_dev(False, K)
     iters_mean = float(it.float().mean().item())
     ok_frac = float((st == 0).float().mean().item())
     slack_frac = float(sl.float().mean().item())
     sat_frac = float(((u0[0].abs() >= 2.0 - 1e-9) | (u0[1].abs() >= 3.0 - 1e-9)).float().mean().item())
-    if world > 1:
-        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
     value = gB * K / (total_ms * 1e-3)
+    Kf = max(5, min(K, 50))
+    full_ms, _, _, _ = timed_dev(True, Kf)
+    value_full = gB * Kf / (full_ms * 1e-3)
 
-    # ---- e2e: the C-ABI host entry point, pinned host buffers, H2D + kernel + D2H per step ---------
-    h_u0 = torch.empty((B, 2), dtype=torch.float64).pin_memory()
-    h_cost = torch.empty(B, dtype=torch.float64).pin_memory()
-    h_st, h_it, h_sl = (torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(3))
+    # ---- e2e: the C-ABI host entry points, pinned host buffers, H2D + kernels + D2H per step -------------------
+    # (a) table form, asynchronous (two calls in flight): each instance's reference segment is
+    #     get_trajectory_segment(k0, N+1) of ONE shared table -- what every caller of the reference does before
+    #     solve_with_ltv (run_simulation.py:247) -- gathered on the device: 148 B per instance cross PCIe;
+    # (b) the same, synchronous; (c) materialised segments (968 B per instance), synchronous, as in round 1.
+    outs = [dict(u0=torch.empty((B, 2), dtype=torch.float64).pin_memory(), cost=torch.empty(B, dtype=torch.float64).pin_memory(),
+                 st=torch.empty(B, dtype=torch.int32).pin_memory(), it=torch.empty(B, dtype=torch.int32).pin_memory(),
+                 sl=torch.empty(B, dtype=torch.int32).pin_memory()) for _ in range(2)]
+
+    def step_table(s, name):
+        h, o = host_sets[s % R], outs[s % 2]
+        ctx.call(name, B, C.byref(prm), h_table.data_ptr(), table.shape[0], tab_sets[s % R].data_ptr(), h[0].data_ptr(),
+                 h[3].data_ptr(), None, o["u0"].data_ptr(), o["cost"].data_ptr(), o["st"].data_ptr(), o["it"].data_ptr(),
+                 o["sl"].data_ptr(), None, None)
 
     def step_host(s):
-        h = host_sets[s % R]
+        h, o = host_sets[s % R], outs[s % 2]
         ctx.call("b2c_mpc_host", B, C.byref(prm), h[0].data_ptr(), h[1].data_ptr(), h[2].data_ptr(),
-                 h[3].data_ptr(), None, h_u0.data_ptr(), h_cost.data_ptr(), h_st.data_ptr(),
-                 h_it.data_ptr(), h_sl.data_ptr(), None, None)
+                 h[3].data_ptr(), None, o["u0"].data_ptr(), o["cost"].data_ptr(), o["st"].data_ptr(),
+                 o["it"].data_ptr(), o["sl"].data_ptr(), None, None)
+
+    def timed_host(fn, steps, wait):
+        for s in range(3):
+            fn(s)
+        if wait:
+            ctx.call("b2c_wait")
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(steps):
+            fn(s)
+        if wait:
+            ctx.call("b2c_wait")
+        barrier()
+        return allmax(time.perf_counter() - t0)
 
     Ke = max(5, min(K, 50))
-    for s in range(3):
-        step_host(s)
-    barrier()
-    t0 = time.perf_counter()
-    for s in range(Ke):
-        step_host(s)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    e2e_async_s = timed_host(lambda s: step_table(s, "b2c_mpc_table_host_async"), Ke, True)
+    e2e_sync_s = timed_host(lambda s: step_table(s, "b2c_mpc_table_host"), Ke, False)
+    last = (Ke - 1)
+    res_table = outs[last % 2]["u0"].clone()
+    e2e_mat_s = timed_host(step_host, Ke, False)
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    e2e_value = gB * Ke / e2e_s
-    h2d = B * (3 + 3 * (N + 1) + 2 * N + 3 * M) * 8
+    h2d_table = B * (3 * 8 + 3 * M * 8 + 4) + table.size * 8
+    h2d_mat = B * (3 + 3 * (N + 1) + 2 * N + 3 * M) * 8
     d2h = B * (2 * 8 + 8 + 3 * 4)
-    # the e2e result must equal the device-resident result for the same batch
-    step_dev((Ke - 1) % R)
+    # every path must return the device-resident result for the same batch, bit for bit
+    step_dev(last % R)
     torch.cuda.synchronize()
-    assert torch.equal(u0.t().cpu(), h_u0), "e2e and device-resident results differ"
+    assert torch.equal(u0.t().cpu(), outs[last % 2]["u0"]), "materialised e2e and device-resident results differ"
+    assert torch.equal(u0.t().cpu(), res_table), "table-form e2e and device-resident results differ"
+
+    c5 = None
+    if not args.no_config5:
+        c5 = config5_leg(ctx, dev, rank, world, args.config5_robots, args.config5_ticks)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant (only) kernel -----------------------------------------------------
+    # ---- rooflines of the dominant kernel ------------------------------------------------------------------------
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    hbm_peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    traffic = None                  # dram bytes per launch of the dominant kernel, from the committed ncu capture
-    try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_slots_traffic.json")))
-        if args.engine != 1 and tr.get("instances_per_launch") == B:
-            traffic = tr["dram_bytes_per_launch"]
+    hbm_peak, which = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+    traffic, traffic_note = None, "no capture committed for this kernel source"
+    try:                          # dram bytes per launch from the committed ncu capture -- only if taken from THIS kernel source
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r2_slots_traffic.json")))
+        if args.engine != 1 and tr.get("instances_per_launch") == B and tr.get("kernel_src_sha") == kernel_src_sha():
+            traffic, traffic_note = tr["dram_bytes_per_launch"], f"ncu --set full capture {tr.get('capture', '')}, kernel source {tr['kernel_src_sha']}"
+        else:
+            traffic_note = f"committed capture is of kernel source {tr.get('kernel_src_sha')}, this build is {kernel_src_sha()}: stale, dropped"
     except Exception:
         pass
     avg_launch_s = float(per_launch_ms.mean()) * 1e-3
@@ -364,41 +468,60 @@ def run_gpu(args):
         n_s = max(128, 32 * cores)
         v_cpu, dt_cpu, u_cpu = cpu_arm(n_s, 100, pool, global_batch=gB)   # = dev_sets[0][:n_s]
         pool.close()
+        v_one, dt_one, _ = cpu_arm(48, 101, None)
         step_dev(0)
         torch.cuda.synchronize()
         parity = float(np.abs(u0.t().cpu().numpy()[:n_s] - u_cpu).max())
         cpu = {"value": v_cpu, "unit": "solves/s", "cores": cores, "kind": "port",
-               "sample": f"first {n_s} instances of the timed batch ({dt_cpu:.1f} s); oracle port of solve_with_ltv "
-                         "(HiGHS + KKT polish); cvxpy/OSQP absent from the image",
+               "sample": f"first {n_s} instances of the timed batch ({dt_cpu:.1f} s) on {cores} cores; 48 instances on 1 core "
+                         f"({dt_one:.1f} s); oracle port of solve_with_ltv (HiGHS + KKT polish); cvxpy/OSQP absent from the image",
+               "value_1_core": v_one,
+               "reference_shipped_log_ms_per_solve": 82.6,
+               "reference_shipped_log_note": "logs/controls_20260208_014109.csv: CVXPY+OSQP on the authors' PC at the SMALLER "
+                                             "N=6 / block 2 / M=3 shape, mean of 200 solves (= 12 solves/s)",
                "max_abs_u0_diff_vs_gpu": parity}
 
     secondary = None
     if world == 1 and not args.no_secondary:
-        secondary = secondary_metrics(ctx, dev, stream)
+        secondary = secondary_metrics(ctx, dev, stream, with_cpu=not args.no_cpu)
 
     line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "instances_per_gpu": B, "global_instances": gB,
-                       "l2": f"inputs rotate over {R} distinct batches ({R}x{h2d / 1e6:.0f} MB > 126 MB L2); kernel scratch "
+                       "l2": f"inputs rotate over {R} distinct batches ({R}x{h2d_mat / 1e6:.0f} MB > 126 MB L2); kernel scratch "
                              f"{nat.load_library().b2c_mpc_scratch_bytes(C.byref(prm), B) / 1e6:.0f} MB",
                        "parallelism": f"batch-sharded x{world}, no data-path collective"},
             "p99_batch_latency_ms": float(np.percentile(per_launch_ms, 99)),
             "p50_batch_latency_ms": float(np.percentile(per_launch_ms, 50)),
+            "value_full_outputs": {"value": value_full, "unit": "solves/s", "ms_per_step": full_ms / Kf, "steps": Kf,
+                                   "alg_bytes_per_solve": ALG_BYTES_FULL,
+                                   "note": "control_sequence + predicted_states written, per-instance step_count supplied "
+                                           "(what MPCController.solve_with_ltv always returns, mpc_controller.py:511-520)"},
             "solver": {"mean_newton_iters": iters_mean, "optimal_frac": ok_frac, "slack_active_frac": slack_frac,
                        "saturated_u0_frac": sat_frac},
-            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": which,
+            "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": achieved_tf / fp64_peak, "traffic": traffic, "traffic_note": traffic_note,
+                         "peak_source": "FMA microbenchmark in this run (b2c_measure_fma_peak; MEASURED_PEAKS.json has no FP64 entry)",
                          "kernel": kernel_name, "avg_launch_ms": avg_launch_s * 1e3,
-                         "alg_bytes_per_solve": ALG_BYTES_PER_SOLVE},
-            "fp64": {"achieved_tflops": achieved_tf, "peak_tflops_measured": fp64_peak,
-                     "frac": achieved_tf / fp64_peak, "fp32_peak_tflops_measured": fp32_peak,
-                     "flop_per_solve_counted": flop_per_solve},
-            "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke, "api": "b2c_mpc_host (C ABI, pinned host buffers)"},
+                         "flop_per_solve_counted": flop_per_solve, "fp32_peak_tflops_measured": fp32_peak,
+                         "why": "29 flop/B against a machine balance of 5 flop/B: FP64 is the binding roof, HBM is reported beside it"},
+            "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": achieved_gbs / hbm_peak, "peak_source": which,
+                             "alg_bytes_per_solve": ALG_BYTES_PER_SOLVE},
+            "e2e": {"value": gB * Ke / e2e_async_s, "unit": "solves/s", "h2d_bytes_per_step": h2d_table, "d2h_bytes_per_step": d2h,
+                    "steps": Ke, "ms_per_step": 1e3 * e2e_async_s / Ke,
+                    "api": "b2c_mpc_table_host_async + b2c_wait (C ABI, pinned host buffers, two calls in flight): shared "
+                           "reference table + per-instance start row, segments gathered on the device",
+                    "sync_value": gB * Ke / e2e_sync_s, "sync_ms_per_step": 1e3 * e2e_sync_s / Ke},
+            "e2e_materialised": {"value": gB * Ke / e2e_mat_s, "unit": "solves/s", "h2d_bytes_per_step": h2d_mat,
+                                 "d2h_bytes_per_step": d2h, "steps": Ke, "ms_per_step": 1e3 * e2e_mat_s / Ke,
+                                 "api": "b2c_mpc_host (C ABI, pinned host buffers): every instance ships its own (N+1)-row segment"},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
             "wall_s_timed_region": t_wall}
+    if c5 is not None:
+        line["config5"] = c5
     if cpu is not None:
         line["cpu_baseline"] = cpu
     if secondary is not None:
@@ -414,8 +537,11 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary (DARE / linearize / rollout) figures")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary (DARE / linearize / latency) figures")
+    ap.add_argument("--no-config5", action="store_true", help="skip the config-5 closed-loop rollout leg")
+    ap.add_argument("--config5-robots", type=int, default=1 << 20, help="robots per GPU of the config-5 leg")
+    ap.add_argument("--config5-ticks", type=int, default=500)
     ap.add_argument("--engine", type=int, default=0, choices=[0, 1, 2],
                     help="K3 kernel: 0 auto (slot kernel for this shape), 1 general kernel, 2 slot kernel")
     args = ap.parse_args()

@@ -41,12 +41,13 @@ def config3_points(B, stress=False, seed=0, A=2.0, a=0.5):
 
 
 def config4_instances(B, N=20, seed=0, start=0, count=None, obstacles=DENSE_OBSTACLES,
-                      pos_jitter=0.1, th_jitter=0.2, obs_jitter=0.2):
+                      pos_jitter=0.1, th_jitter=0.2, obs_jitter=0.2, return_k0=False):
     """MPC instances [start, start+count) of a global batch of B (instance-major arrays).
 
     Per instance: k0 ~ U{0..979}; (x_refs, u_refs) = segment(k0, N+1) of generate(20.0);
     x0 = x_refs[0] + U(+-.1, +-.1, +-.2); the obstacle set shifted by U(+-.2)^2 per obstacle.
-    Returns x0 (n,3), x_refs (n,N+1,3), u_refs (n,N,2), obs (n,M,3)."""
+    Returns x0 (n,3), x_refs (n,N+1,3), u_refs (n,N,2), obs (n,M,3) [, k0 (n,) int32: x_refs / u_refs are
+    get_trajectory_segment(k0, N+1) of figure8_table()]."""
     count = B - start if count is None else count
     table = figure8_table()
     rng = np.random.default_rng(seed)
@@ -62,6 +63,8 @@ def config4_instances(B, N=20, seed=0, start=0, count=None, obstacles=DENSE_OBST
     x0 = x_refs[:, 0, :] + dx0[sl]
     obs = np.broadcast_to(np.asarray(obstacles, float)[None], (count, M, 3)).copy()
     obs[:, :, :2] += dob[sl]
+    if return_k0:                 # the table form of the entry points takes (table, k0) instead of the segments
+        return x0, x_refs, u_refs, obs, k0[sl].astype(np.int32)
     return x0, x_refs, u_refs, obs
 
 

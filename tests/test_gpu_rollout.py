@@ -106,3 +106,27 @@ def test_rollout_without_obstacles_and_single_robot():
     assert a["mpc_solves"][0] == 0 and a["switches"][0] == 0 and a["lqr_steps"][0] == 200
     assert np.array_equal(a["states"], b["states"]) and np.array_equal(a["controls"], b["controls"])
     assert (a["risk"] == 0).all() and a["collision_states"][0] == 0
+
+
+def test_config5_device_generator_and_shard_invariance():
+    """BASELINE config 5 inputs are generated ON THE DEVICE from (seed, global robot index): the device generator equals
+    its numpy mirror bit for bit, and a 2-way split of 4,096 robots (two calls, as two ranks would make them) equals the
+    unsplit run bit for bit -- states, counters and statistics."""
+    from hybrid_controller.rollout import simulate_generated_shard, simulate_batch
+    from hybrid_controller import workloads as wl
+    lqr, mpc, risk = _controllers()
+    table = lin_dare.figure8(20.0)
+    R, T, seed = 4096, 60, 5
+    kw = dict(lqr=lqr, mpc=mpc, risk=risk)
+    full = simulate_generated_shard(R, 0, seed, table, T, return_inputs=True, **kw)
+    k0, x0, ob = wl.config5_robots(R, 0, seed, table=table)
+    assert np.array_equal(full["inputs"][0], k0) and np.array_equal(full["inputs"][1], x0)
+    assert np.array_equal(full["inputs"][2], ob)
+    assert k0.min() >= 0 and k0.max() <= 499 and np.abs(x0 - table[k0, 1:4]).max() <= 0.2
+    halves = [simulate_generated_shard(R // 2, h * (R // 2), seed, table, T, **kw) for h in range(2)]
+    for k in ("x", "lqr_steps", "mpc_solves", "switches", "collision_states", "mpc_fallbacks", "mean_error", "max_error"):
+        assert np.array_equal(np.concatenate([h[k] for h in halves]), full[k]), k
+    assert full["mpc_solves"].sum() > 0 and full["lqr_steps"].sum() > 0 and full["mpc_fallbacks"].sum() == 0
+    # and the engine fed the mirrored inputs through the host entry point gives the same robots
+    ref = simulate_batch("hybrid", table, k0[:512], x0[:512], ob[:512], T, **kw)
+    assert np.array_equal(ref["x"], full["x"][:512]) and np.array_equal(ref["mpc_solves"], full["mpc_solves"][:512])

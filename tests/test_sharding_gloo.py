@@ -73,3 +73,52 @@ def test_shard_range_partitions():
             assert spans[0][0] == 0 and sum(c for _, c in spans) == Bn
             for (s0, c0), (s1, _) in zip(spans, spans[1:]):
                 assert s0 + c0 == s1
+
+
+# ---- config 5 (closed-loop rollouts): robots keyed by global index, rollout statistics all-reduced ----------------
+R5, T5 = 96, 40
+
+
+def _controllers5():
+    from hybrid_controller.controllers import LQRController, MPCController, RiskMetrics
+    from hybrid_controller import workloads as wl
+    return dict(lqr=LQRController(**wl.SIM_LQR), mpc=MPCController(horizon=6, block_size=1, **wl.SIM_MPC),
+                risk=RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2, threshold_medium=0.5))
+
+
+def _rank_main5(rank, world, port, outdir):
+    for p in (ROOT, PKG, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import emul as em
+    from hybrid_controller import workloads as wl, dist_stats
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    start, count = wl.shard_range(R5, rank, world)
+    table = wl.figure8_table()
+    k0, x0, ob = wl.config5_robots(count, first_index=start, seed=9, table=table)
+    out = em.rollout("hybrid", table, k0, x0, ob, T5, **_controllers5())
+    st = dist_stats.reduce_stats(dist_stats.rollout_stats(out, T5))
+    np.savez(os.path.join(outdir, f"q{rank}.npz"), start=start, count=count, x=out["x"], mpc=out["mpc_solves"], **st)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_config5_sharded_rollout_equals_single(tmp_path):
+    from hybrid_controller import workloads as wl, dist_stats
+    world = 2
+    port = 31500 + (os.getpid() % 2000)
+    mp.start_processes(_rank_main5, args=(world, port, str(tmp_path)), nprocs=world, join=True, start_method="fork")
+    table = wl.figure8_table()
+    k0, x0, ob = wl.config5_robots(R5, first_index=0, seed=9, table=table)
+    full = emul.rollout("hybrid", table, k0, x0, ob, T5, **_controllers5())
+    ref = dist_stats.rollout_stats(full, T5)
+    assert ref["mpc_solves"] > 0 and ref["lqr_steps"] > 0
+    for r in range(world):
+        d = np.load(os.path.join(tmp_path, f"q{r}.npz"))
+        s, c = int(d["start"]), int(d["count"])
+        assert np.array_equal(d["x"], full["x"][s:s + c]) and np.array_equal(d["mpc"], full["mpc_solves"][s:s + c])
+        for k in ("robots", "robot_steps", "lqr_steps", "mpc_solves", "switches", "collision_states", "mpc_fallbacks"):
+            assert int(d[k]) == int(ref[k]), k
+        assert abs(float(d["err_mean_sum"]) - float(ref["err_mean_sum"])) <= 1e-9 * float(ref["err_mean_sum"])
+        assert float(d["err_max"]) == float(ref["err_max"])
