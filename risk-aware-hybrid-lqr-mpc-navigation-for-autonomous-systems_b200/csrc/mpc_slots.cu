@@ -540,24 +540,43 @@ B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
         u00 = ur00 + MW(0); u01 = ur01 + MW(1);
         Jout = s.J;
         if (a.useq || a.xpred) {                  // add the (wrapped) references back, :497-498
+            // four stages of record / heading loads in flight together (one L2 round trip per four stages); the
+            // record holds the reference position and inputs the caller passed, so only the heading is re-read
             double zx = s.z0x, zy = s.z0y, zt = s.z0t;
-            for (int k = 0; k <= N; ++k) {
-                if (a.xpred) {
-                    a.xpred[mpc_out_x(a, i, k, 0)] = zx + mpc_in_xref(a, i, k, 0);
-                    a.xpred[mpc_out_x(a, i, k, 1)] = zy + mpc_in_xref(a, i, k, 1);
-                    a.xpred[mpc_out_x(a, i, k, 2)] = zt + mpc_in_xref(a, i, k, 2);
+            constexpr int C = 4;
+            for (int k0 = 0; k0 < N; k0 += C) {
+                Stage6 g6[C]; double thr[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const int k = (k0 + c < N) ? (k0 + c) : (N - 1);
+                    g6[c] = g_load(m, k);
+                    thr[c] = a.xpred ? mpc_in_xref(a, i, k, 2) : 0.0;
                 }
-                if (k == N) break;
-                const double wk0 = MW(2 * k), wk1 = MW(2 * k + 1);
-                double ck, sk, uo0, uo1;
-                g_load4(m, k, ck, sk, uo0, uo1);
-                if (a.useq) {
-                    a.useq[mpc_out_u(a, i, k, 0)] = wk0 + uo0;
-                    a.useq[mpc_out_u(a, i, k, 1)] = wk1 + uo1;
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const int k = k0 + c;
+                    if (k < N) {
+                        if (a.xpred) {
+                            a.xpred[mpc_out_x(a, i, k, 0)] = zx + g6[c].prx;
+                            a.xpred[mpc_out_x(a, i, k, 1)] = zy + g6[c].pry;
+                            a.xpred[mpc_out_x(a, i, k, 2)] = zt + thr[c];
+                        }
+                        const double wk0 = MW(2 * k), wk1 = MW(2 * k + 1);
+                        if (a.useq) {
+                            a.useq[mpc_out_u(a, i, k, 0)] = wk0 + g6[c].uo0;
+                            a.useq[mpc_out_u(a, i, k, 1)] = wk1 + g6[c].uo1;
+                        }
+                        const double vr = b2c_guard_v(g6[c].uo0, B2C_GUARD_MPC);
+                        const double nzx = zx + (-vr * g6[c].sk) * zt + g6[c].ck * wk0;
+                        const double nzy = zy + (vr * g6[c].ck) * zt + g6[c].sk * wk0;
+                        zt = zt + a.dt * wk1; zx = nzx; zy = nzy;
+                    }
                 }
-                const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
-                const double nzx = zx + (-vr * sk) * zt + ck * wk0, nzy = zy + (vr * ck) * zt + sk * wk0;
-                zt = zt + a.dt * wk1; zx = nzx; zy = nzy;
+            }
+            if (a.xpred) {
+                a.xpred[mpc_out_x(a, i, N, 0)] = zx + mpc_in_xref(a, i, N, 0);
+                a.xpred[mpc_out_x(a, i, N, 1)] = zy + mpc_in_xref(a, i, N, 1);
+                a.xpred[mpc_out_x(a, i, N, 2)] = zt + mpc_in_xref(a, i, N, 2);
             }
         }
         if (sc < a.ramp_up_steps) {               // cold-start ramp, :500-507
@@ -755,13 +774,15 @@ k_mpc_slots(const MpcArgs a) {
     unsigned long long cum0 = 0, cum1 = 0, cum2 = 0;          // class boundaries in queue order
     if (a.perm) { cum0 = a.class_count[0]; cum1 = cum0 + a.class_count[1]; cum2 = cum1 + a.class_count[2]; }
     int64_t seen = 0;                                         // queue position at this warp's last claim
-    TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;)
+    TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;
+          long long tr_undo = 0, tr_team = 0, tr_sweep = 0, tr_post = 0, tr_teamrounds = 0, tr_c2 = 0, tr_tb = 0, tr_tf = 0, tr_bact = 0;)
     for (;;) {
         TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE));)
         // ---- backward phase -----------------------------------------------------------------------------
         {
             const bool act = (s.mode == SLOT_BWD);
             if (__any_sync(FULL, act)) {
+                TRACE(++tr_bact;)
                 const double dec = slot_backward<SS, MT, KT>(a, m, s, act);
                 if (act) slot_backward_post<SS, MT>(a, m, s, dec);
             }
@@ -830,6 +851,7 @@ k_mpc_slots(const MpcArgs a) {
                 s.undo = 0;
             }
         }
+        TRACE(__syncwarp(); tr_undo += clock64() - tr_c; tr_c2 = clock64();)
         const bool gain = (s.mode == SLOT_FWD_GAIN);
         const unsigned idle_m = __ballot_sync(FULL, s.mode == SLOT_IDLE);
         const bool team_round = (idle_m != 0u) && (req_m != 0u);          // warp-uniform
@@ -883,6 +905,7 @@ k_mpc_slots(const MpcArgs a) {
             if (__any_sync(FULL, hopen)) slot_undo<SS, KT>(a, m, false, hopen);
             __syncwarp();
         }
+        TRACE(__syncwarp(); tr_team += clock64() - tr_c2; tr_c2 = clock64(); if (team_round) ++tr_teamrounds;)
         const bool plain = (s.mode == SLOT_FWD_PLAIN);
         const bool run = gain || plain || helper;
         const bool fgain = gain || helper;
@@ -890,6 +913,7 @@ k_mpc_slots(const MpcArgs a) {
         if (__any_sync(FULL, run))
             Jn = slot_forward<SS, MT, KT>(a, m, fz0x, fz0y, fz0t, falpha, run, fgain, plain, __any_sync(FULL, fgain), mv, lx, ly, lt);
         __syncwarp();
+        TRACE(tr_sweep += clock64() - tr_c2; tr_c2 = clock64();)
         int krej = 1;
         bool handled = false;                                             // my instance moved to a helper's lane
         if (team_round) {
@@ -925,13 +949,15 @@ k_mpc_slots(const MpcArgs a) {
         m.g = own_g;
         if (!handled && !helper && run) slot_forward_post<SS, MT>(a, m, s, gain, Jn, mv, lx, ly, lt, krej);
         __syncwarp();
-        TRACE(tr_f += clock64() - tr_c;)
+        TRACE(tr_f += clock64() - tr_c; tr_post += clock64() - tr_c2;
+              if (team_round) { tr_tf += clock64() - tr_c; })
     }
     TRACE(if (lane == 0) {
         const int w = (blockIdx.x * SS + threadIdx.x) >> 5;
         if (w < 8192) {
             unsigned long long* t = g_slot_trace + 16 * w;
             t[0] = tr_t0; t[1] = trace_ns(); t[2] = tr_rounds; t[3] = tr_b; t[4] = tr_r; t[5] = tr_f; t[6] = tr_lanes; t[7] = 1;
+            t[8] = tr_undo; t[9] = tr_team; t[10] = tr_sweep; t[11] = tr_post; t[12] = tr_teamrounds; t[13] = tr_tf; t[14] = tr_bact;
         }
     })
     if (KT > 0) {

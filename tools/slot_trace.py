@@ -60,6 +60,13 @@ def main():
                              "refill": float(cyc[:, 1].sum() / rounds.sum()),
                              "forward": float(cyc[:, 2].sum() / rounds.sum())},
         "slots_cfg": os.environ.get("B2C_SLOTS_CFG", "auto"),
+        "forward_phase_cycles_per_round": dict(zip(("undo", "team_setup", "sweep", "post"), (t[:, 8:12].sum(axis=0) / rounds.sum()).tolist())),
+        "team_rounds_frac": float(t[:, 12].sum() / rounds.sum()),
+        "forward_cycles_per_team_round": float(t[:, 13].sum() / max(t[:, 12].sum(), 1)),
+        "backward_sweeps_per_round": float(t[:, 14].sum() / rounds.sum()),
+        "slowest_warps": [dict(end_us=float((r[1] - t0) / 1e3), rounds=int(r[2]), bwd=int(r[3]), refill=int(r[4]), fwd=int(r[5]),
+                               undo=int(r[8]), team=int(r[9]), sweep=int(r[10]), post=int(r[11]), team_rounds=int(r[12]),
+                               bwd_sweeps=int(r[14])) for r in t[np.argsort(-t[:, 1])[:4]]],
         "us_per_round_mean": float(((t[:, 1] - t[:, 0]) / 1e3).sum() / rounds.sum()),
     }))
 
