@@ -89,12 +89,23 @@ __device__ __forceinline__ void tm_st16(uint32_t taddr, const double (&u)[8]) {
 // a tcgen05.st is complete (visible to a later tcgen05.ld of the same thread) only after wait::st
 __device__ __forceinline__ void tm_fence_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 #endif
+// `d`: lane offset of the strip that is read (0 = this lane's own; a helper lane reads its team owner's strip in
+// place); `srcl` / `team`: for the stages in tensor memory, which is lane-private, the owner's values come by shuffle
+// (team is warp-uniform: every lane takes part in the shuffles).
 template <int SS, int KT>
-B2C_HD void u_load8(const SlotMem& m, int k, double (&u)[8]) {
+B2C_HD void u_load8(const SlotMem& m, int k, double (&u)[8], const int d = 0, const int srcl = 0, const bool team = false) {
 #if defined(__CUDA_ARCH__)
-    if (KT > 0 && k < KT) { tm_ld16(m.tm + 16u * (uint32_t)k, u); return; }
+    if (KT > 0 && k < KT) {
+        tm_ld16(m.tm + 16u * (uint32_t)k, u);
+        if (team) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) u[e] = __shfl_sync(0xffffffffu, u[e], srcl);
+        }
+        return;
+    }
 #endif
-    const double* p = m.us + (size_t)(8 * (k - KT)) * SS;
+    (void)srcl; (void)team;
+    const double* p = m.us + (ptrdiff_t)(8 * (k - KT)) * SS + d;
 #pragma unroll
     for (int e = 0; e < 8; ++e) u[e] = p[(size_t)e * SS];
 }
@@ -192,8 +203,7 @@ struct SlotState {
     int mode, it, ls, st;
     double alpha, J, dec, z0x, z0y, z0t, lamx, lamy, lamt, max_viol;
     int rej;                                          // a trial step of this solve has been rejected (kernel: asks for helper lanes)
-    int undo;                                         // a rejected trial is still to be undone: 1 = inputs and gains from the
-                                                      // mirrors, 2 = and the gains rewritten as the open-loop direction (arc)
+    int undo;                                         // a rejected trial is still to be undone (inputs and gains from the mirrors)
 };
 
 // ----- difficulty classes (work ordering only; never changes a result) ------------------------------
@@ -293,20 +303,33 @@ B2C_HD void slot_row(const MpcArgs& a, double ddx, double ddy, double d2, double
 template <int SS, int MT, int KT>
 B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x, const double z0y, const double z0t,
                            const double alpha_, const bool act, const bool gain, const bool fresh, const bool any_gain,
-                           double& max_viol, double& lamx, double& lamy, double& lamt) {
+                           double& max_viol, double& lamx, double& lamy, double& lamt,
+                           const bool arc = false, const bool any_arc = false,
+                           const int dW = 0, const int dU = 0, const int srcU = 0, const bool team = false) {
+    // arc (per lane; any_arc warp-uniform): from the MPC_LS_CLOSED-th rejected trial of an iteration on, the trial is
+    // Bertsekas' projection arc P[w + alpha d] along the OPEN-LOOP Newton direction of the linear model,
+    // d_j = -kf_j - K_j dz_j, dz_{j+1} = A dz_j + B d_j, which descends for small alpha because frozen inputs are
+    // decoupled in Quu.  d is built stage by stage from the gains and the stage constants the sweep holds anyway.
+    // team (warp-uniform): helper lanes evaluate trial steps of another lane's instance and read that lane's W / OB
+    // strips (lane offset dW) and gains (offset dU, or by shuffle from lane srcU for the stages in tensor memory) IN
+    // PLACE; everything a lane writes goes to its own strips.  The owner updates W and U in place as the sweep
+    // advances: a __syncwarp per stage keeps its writes behind every lane's reads of that stage.
+    const double* const wsrc = m.w + dW;
+    const double* const osrc = m.ob + dW;
     const int N = a.N, M = (MT >= 0) ? MT : a.M;
     constexpr int MR = (MT > 0) ? MT : 1;
     double OX[MR], OY[MR], OC[MR], OCC[MR];
     if (MT > 0) {
 #pragma unroll
         for (int mm = 0; mm < MR; ++mm) {
-            OX[mm] = MO(3 * mm); OY[mm] = MO(3 * mm + 1); OC[mm] = MO(3 * mm + 2);
+            OX[mm] = osrc[(3 * mm) * SS]; OY[mm] = osrc[(3 * mm + 1) * SS]; OC[mm] = osrc[(3 * mm + 2) * SS];
             OCC[mm] = OC[mm] * fabs(OC[mm]);
         }
     }
     double zx = z0x, zy = z0y, zt = z0t;              // new trajectory
     double ox = zx, oy = zy, ot = zt;                 // old trajectory
     double J = 0.0, mv = 0.0;
+    double ldx = 0.0, ldy = 0.0, ldth = 0.0;          // arc: deviation of the linear model along d
     const double alpha = gain ? alpha_ : 0.0;
     ring_issue<SS>(m, 0, act, 0.0);
     ring_issue<SS>(m, 1, act && N > 1, 0.0);
@@ -315,15 +338,30 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         const double ck = cur.ck, sk = cur.sk, uo0 = cur.uo0, uo1 = cur.uo1, prx = cur.prx, pry = cur.pry;
         ring_issue<SS>(m, k + 2, act && k + 2 < N, ck + pry);       // constants two stages ahead
         double u[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        if (any_gain) u_load8<SS, KT>(m, k, u);       // the gains of this stage (any_gain: warp-uniform)
+        if (any_gain) u_load8<SS, KT>(m, k, u, dU, srcU, team);       // the gains of this stage (any_gain: warp-uniform)
         const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
-        const double wo0 = fresh ? b2c_clip(0.0, lb0, ub0) : MW(2 * k);
-        const double wo1 = fresh ? b2c_clip(0.0, lb1, ub1) : MW(2 * k + 1);
+        const double wo0 = fresh ? b2c_clip(0.0, lb0, ub0) : wsrc[(2 * k) * SS];
+        const double wo1 = fresh ? b2c_clip(0.0, lb1, ub1) : wsrc[(2 * k + 1) * SS];
+#ifdef __CUDA_ARCH__
+        if (team) __syncwarp();                       // every lane has read stage k of the strips it borrows
+#endif
         double w0 = wo0, w1 = wo1;
         if (gain) {
             const double dx = zx - ox, dy = zy - oy, dth = zt - ot;
             w0 = wo0 - alpha * u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
             w1 = wo1 - alpha * u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
+            if (any_arc) {
+                if (arc) {
+                    const double d0 = -u[6] - (u[0] * ldx + u[1] * ldy + u[2] * ldth);
+                    const double d1 = -u[7] - (u[3] * ldx + u[4] * ldy + u[5] * ldth);
+                    w0 = wo0 + alpha * d0;
+                    w1 = wo1 + alpha * d1;
+                    const double vra = b2c_guard_v(uo0, B2C_GUARD_MPC);
+                    const double nldx = ldx + (-vra * sk) * ldth + ck * d0;
+                    const double nldy = ldy + (vra * ck) * ldth + sk * d0;
+                    ldth = ldth + a.dt * d1; ldx = nldx; ldy = nldy;
+                }
+            }
             w0 = b2c_clip(w0, lb0, ub0);
             w1 = b2c_clip(w1, lb1, ub1);
         }
@@ -350,12 +388,12 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
                 int mm = 0; while (!((hit >> mm) & 1u)) ++mm;
 #endif
                 hit &= hit - 1u;
-                const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1);
-                slot_row(a, ddx, ddy, ddx * ddx + ddy * ddy, MO(3 * mm + 2), zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
+                const double ddx = prx - osrc[(3 * mm) * SS], ddy = pry - osrc[(3 * mm + 1) * SS];
+                slot_row(a, ddx, ddy, ddx * ddx + ddy * ddy, osrc[(3 * mm + 2) * SS], zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
             }
         } else if (MT < 0) {
             for (int mm = 0; mm < M; ++mm) {
-                const double ddx = prx - MO(3 * mm), ddy = pry - MO(3 * mm + 1), c = MO(3 * mm + 2);
+                const double ddx = prx - osrc[(3 * mm) * SS], ddy = pry - osrc[(3 * mm + 1) * SS], c = osrc[(3 * mm + 2) * SS];
                 const double d2 = ddx * ddx + ddy * ddy;
                 const double q = d2 + ddx * zx + ddy * zy;
                 if (act && (d2 > 1e-4) && (c * fabs(c) * d2 > q * fabs(q)))
@@ -472,31 +510,23 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
 // ----- undo a rejected trial -------------------------------------------------------------------------
 // Deferred to the start of the next forward phase and run by the whole warp (U accesses are warp-uniform): `pred`
 // lanes take their previous inputs back from GW and their gains from the mirror GG (what happened to their U strip
-// in between does not matter); `open_loop` lanes (from the MPC_LS_CLOSED-th rejection of an iteration on) then
-// rewrite the gains as the OPEN-LOOP Newton direction of the linear model (d_j = -kf_j - K_j dz_j,
-// dz_{j+1} = A dz_j + B d_j) so that the next trial is Bertsekas' projection arc P[w + alpha d], which descends for
-// small alpha because frozen inputs are decoupled in Quu.  Other lanes keep their U.  The stage constants of the
-// open-loop pass come straight from the record (L2).
+// in between does not matter).  Other lanes keep their U.  Four stages of mirror loads are in flight together (one
+// L2 round trip per four stages instead of one per stage).
 template <int SS, int KT>
-B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred, const bool open_loop) {
+B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred) {
     const int N = a.N;
-    constexpr int C = 4;                              // stages whose mirror / record loads are in flight together: one L2
-                                                      // round trip per four stages instead of one per stage
-    double dx = 0.0, dy = 0.0, dth = 0.0;
+    constexpr int C = 4;
     for (int j0 = 0; j0 < N; j0 += C) {
         double2 wp[C], q0[C], q1[C], q2[C], q3[C];
-        double ck[C], sk[C], uo0[C], uo1[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) {
             const int j = (j0 + c < N) ? (j0 + c) : (N - 1);
             wp[c] = q0[c] = q1[c] = q2[c] = q3[c] = make_double2(0.0, 0.0);
-            ck[c] = sk[c] = uo0[c] = uo1[c] = 0.0;
             if (pred) {
                 wp[c] = *reinterpret_cast<const double2*>(m.gw + (int64_t)j * 2 * m.gs);
                 const double2* p = reinterpret_cast<const double2*>(m.gg + (int64_t)j * 8 * m.gs);
                 q0[c] = p[0]; q1[c] = p[1]; q2[c] = p[2]; q3[c] = p[3];
             }
-            if (open_loop) g_load4(m, j, ck[c], sk[c], uo0[c], uo1[c]);
         }
 #pragma unroll
         for (int c = 0; c < C; ++c) {
@@ -508,17 +538,6 @@ B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred, const
                     MW(2 * j) = wp[c].x; MW(2 * j + 1) = wp[c].y;
                     u[0] = q0[c].x; u[1] = q0[c].y; u[2] = q1[c].x; u[3] = q1[c].y;
                     u[4] = q2[c].x; u[5] = q2[c].y; u[6] = q3[c].x; u[7] = q3[c].y;
-                }
-                if (open_loop) {
-                    const double d0 = -u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
-                    const double d1 = -u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
-                    const double vr = b2c_guard_v(uo0[c], B2C_GUARD_MPC);
-                    const double ndx = dx + (-vr * sk[c]) * dth + ck[c] * d0;
-                    const double ndy = dy + (vr * ck[c]) * dth + sk[c] * d0;
-                    dth = dth + a.dt * d1; dx = ndx; dy = ndy;
-#pragma unroll
-                    for (int e = 0; e < 6; ++e) u[e] = 0.0;
-                    u[6] = -d0; u[7] = -d1;
                 }
                 u_store8<SS, KT>(m, j, u);
             }
@@ -647,7 +666,7 @@ B2C_HD void slot_forward_post(const MpcArgs& a, const SlotMem& m, SlotState& s, 
     }
     for (int r = 0; r < krej; ++r) s.alpha *= 0.5;    // reject: undo (deferred), shorten (the arc continues from this alpha)
     s.ls += krej; s.rej = 1;
-    s.undo = (s.ls >= MPC_LS_CLOSED) ? 2 : 1;
+    s.undo = 1;
     if (s.ls >= MPC_LS_MAX) {                     // rounding floor or stall
         s.st = (s.dec <= 1e-9 * fmax(1.0, fabs(s.J))) ? B2C_OK : B2C_MAXITER;
         // the outputs are those of the last accepted point: put its inputs back before writing them
@@ -847,7 +866,7 @@ k_mpc_slots(const MpcArgs a) {
         {
             const bool und = (s.undo != 0);
             if (__any_sync(FULL, und)) {
-                slot_undo<SS, KT>(a, m, und, s.undo == 2);
+                slot_undo<SS, KT>(a, m, und);
                 s.undo = 0;
             }
         }
@@ -858,6 +877,7 @@ k_mpc_slots(const MpcArgs a) {
         int ol = lane, off = 0, ols = 0;                                  // team owner, trial offset, owner's trial index
         bool helper = false;
         double fz0x = s.z0x, fz0y = s.z0y, fz0t = s.z0t, falpha = s.alpha, Jref = s.J;
+        int dW = 0, dU = 0, srcU = lane;                                  // strips the forward sweep reads (0 = my own)
         const double* own_g = m.g;
         if (team_round) {
             const int nown = __popc(req_m);
@@ -877,41 +897,21 @@ k_mpc_slots(const MpcArgs a) {
                 for (int r = 0; r < off; ++r) al *= 0.5;
                 falpha = al;
                 m.g = reinterpret_cast<const double*>((uintptr_t)og);
-                const int d = ol - lane;                                  // the owner's shared strips (W, U tail, OB) -> mine
-                int f = 0;                                                // eight loads in flight per store batch
-                for (; f + 8 <= nfields; f += 8) {
-                    double t8[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) t8[e] = m.w[(size_t)(f + e) * SS + d];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) m.w[(size_t)(f + e) * SS] = t8[e];
-                }
-                for (; f < nfields; ++f) m.w[(size_t)f * SS] = m.w[(size_t)f * SS + d];
+                dW = ol - lane;                                           // the owner's W / OB strips, read in place
             }
-            if (KT > 0) {                                                 // the TMEM part of U: by shuffle from the owner's lane
-                const int kt = a.N < KT ? a.N : KT;
-                for (int k = 0; k < kt; ++k) {
-                    double u[8];
-                    u_load8<SS, KT>(m, k, u);
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) { const double t = __shfl_sync(FULL, u[e], ol); u[e] = helper ? t : u[e]; }
-                    u_store8<SS, KT>(m, k, u);
-                }
-                u_fence<KT>();
-            }
-            // a helper whose trial index crosses MPC_LS_CLOSED evaluates the projection arc: its copy of the gains
-            // becomes the open-loop direction
-            const bool hopen = helper && (ols < MPC_LS_CLOSED) && (ols + off >= MPC_LS_CLOSED);
-            if (__any_sync(FULL, hopen)) slot_undo<SS, KT>(a, m, false, hopen);
+            if (helper) { dU = ol - lane; srcU = ol; }                    // and its gains
             __syncwarp();
         }
         TRACE(__syncwarp(); tr_team += clock64() - tr_c2; tr_c2 = clock64(); if (team_round) ++tr_teamrounds;)
         const bool plain = (s.mode == SLOT_FWD_PLAIN);
         const bool run = gain || plain || helper;
         const bool fgain = gain || helper;
+        // trial index MPC_LS_CLOSED and beyond: the projection arc (owner: its own count; helper: the owner's + its offset)
+        const bool arc = helper ? (ols + off >= MPC_LS_CLOSED) : (gain && s.ls >= MPC_LS_CLOSED);
         double Jn = 0.0, mv = 0.0, lx = 0.0, ly = 0.0, lt = 0.0;
         if (__any_sync(FULL, run))
-            Jn = slot_forward<SS, MT, KT>(a, m, fz0x, fz0y, fz0t, falpha, run, fgain, plain, __any_sync(FULL, fgain), mv, lx, ly, lt);
+            Jn = slot_forward<SS, MT, KT>(a, m, fz0x, fz0y, fz0t, falpha, run, fgain, plain, __any_sync(FULL, fgain), mv, lx, ly, lt,
+                                          arc, __any_sync(FULL, arc), dW, dU, srcU, team_round);
         __syncwarp();
         TRACE(tr_sweep += clock64() - tr_c2; tr_c2 = clock64();)
         int krej = 1;
@@ -938,7 +938,11 @@ k_mpc_slots(const MpcArgs a) {
                     s.alpha = falpha; s.ls = ols + off; s.rej = 1; s.undo = 0;
                     s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;
                     s.mode = SLOT_BWD;
-                    own_g = m.g;                                          // the record came with the copy
+                    own_g = m.g;                                          // the record pointer comes with the instance,
+                    {                                                     // and so does its obstacle strip
+                        const int M3 = 3 * ((MT >= 0) ? MT : a.M);
+                        for (int e = 0; e < M3; ++e) MO(e) = m.ob[(size_t)e * SS + dW];
+                    }
                 } else if (moved && lane == ol) {                         // my instance went to lane `win`
                     s.mode = SLOT_IDLE; s.inst = -1; s.rej = 0; s.undo = 0;
                     own_g = nullptr;
@@ -1125,10 +1129,12 @@ static void emul_one(const MpcArgs& a, SlotMem& m, double* rec, int64_t i) {
             slot_backward_post<SS, MT>(a, m, s, dec);
         }
         if (s.mode == SLOT_FWD_GAIN || s.mode == SLOT_FWD_PLAIN) {
-            if (s.undo) { slot_undo<SS, KT>(a, m, true, s.undo == 2); s.undo = 0; }
+            if (s.undo) { slot_undo<SS, KT>(a, m, true); s.undo = 0; }
             const bool gain = (s.mode == SLOT_FWD_GAIN), plain = !gain;
             double mv, lx, ly, lt;
-            const double Jn = slot_forward<SS, MT, KT>(a, m, s.z0x, s.z0y, s.z0t, s.alpha, true, gain, plain, gain, mv, lx, ly, lt);
+            const bool arc = gain && s.ls >= MPC_LS_CLOSED;
+            const double Jn = slot_forward<SS, MT, KT>(a, m, s.z0x, s.z0y, s.z0t, s.alpha, true, gain, plain, gain, mv, lx, ly, lt,
+                                                       arc, arc);
             slot_forward_post<SS, MT>(a, m, s, gain, Jn, mv, lx, ly, lt, 1);
         }
     }
