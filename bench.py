@@ -225,6 +225,29 @@ def secondary_metrics(ctx, dev, stream, with_cpu):
         out["linearize_config3"]["cpu_baseline"] = {"points_per_s_1_core": 65536 / (time.perf_counter() - t0), "cores": 1,
                                                     "kind": "port of get_discrete_model_explicit, Python loop",
                                                     "sample": "65,536 points"}
+    # the throughput regime of K3: 1,048,576 instances per launch (16 x the headline batch): the slot kernel then runs
+    # 256 slots per SM with the U strips in tensor memory (two warps per scheduler) and latency no longer decides
+    nb, blocks = 1 << 20, 16
+    prm = nat.mpc_params(nat.MPC_LTV, HORIZON, N_OBS, 1, [15, 15, 50], [.1, .1], [30, 30, 40], .3, 5000., 2., 3., .02)
+    parts = [wl.config4_instances(B_PER_GPU, N=HORIZON, seed=500 + b) for b in range(blocks)]
+    big = [torch.from_numpy(np.ascontiguousarray(np.concatenate([p_[j] for p_ in parts]).reshape(nb, -1))).to(dev).t().contiguous()
+           for j in range(4)]
+    del parts
+    bu0 = torch.empty((2, nb), dtype=torch.float64, device=dev); bcost = torch.empty(nb, dtype=torch.float64, device=dev)
+    bst, bit, bsl = (torch.empty(nb, dtype=torch.int32, device=dev) for _ in range(3))
+    t = timed(lambda r: ctx.call("b2c_mpc_dev", nb, C.byref(prm), big[0].data_ptr(), big[1].data_ptr(), big[2].data_ptr(),
+                                 big[3].data_ptr(), None, bu0.data_ptr(), bcost.data_ptr(), bst.data_ptr(), bit.data_ptr(),
+                                 bsl.data_ptr(), None, None), 10)
+    I1 = float(bit.float().mean().item())
+    flop1 = HORIZON * (I1 + 1.0) * (FLOP_BWD_STAGE + FLOP_FWD_STAGE)
+    peak64 = ctx.fma_peak(64)
+    out["mpc_1M_instances_per_launch"] = {"instances": nb, "ms": t * 1e3, "solves_per_s": nb / t, "mean_newton_iters": I1,
+                                          "optimal_frac": float((bst == 0).float().mean().item()),
+                                          "fp64_tflops": flop1 * nb / t / 1e12, "fp64_frac": flop1 * nb / t / 1e12 / peak64,
+                                          "hbm_gbs_algorithmic": ALG_BYTES_PER_SOLVE * nb / t / 1e9,
+                                          "kernel": "k_mpc_slots<256, 5, 16>: 256 slots per SM, first 16 stages of the U strips in tensor memory",
+                                          "l2": "1.0 GB of inputs per launch > 126 MB L2"}
+    del big, bu0, bcost, bst, bit, bsl
     # batch = 1 latency through the drop-in class (host numpy in/out, wall clock): run_simulation.py --mode mpc shape
     mpc = MPCController(horizon=6, block_size=2, **wl.SIM_MPC)
     table = wl.figure8_table()
