@@ -340,30 +340,37 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         double u[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         if (any_gain) u_load8<SS, KT>(m, k, u, dU, srcU, team);       // the gains of this stage (any_gain: warp-uniform)
         const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
-        const double wo0 = fresh ? b2c_clip(0.0, lb0, ub0) : wsrc[(2 * k) * SS];
-        const double wo1 = fresh ? b2c_clip(0.0, lb1, ub1) : wsrc[(2 * k + 1) * SS];
+        // selects, not branches: the common path of a stage stays one basic block (a lone warp on its scheduler lives
+        // off the instruction-level parallelism the compiler finds inside it)
+        const double ws0 = wsrc[(2 * k) * SS], ws1 = wsrc[(2 * k + 1) * SS];
+        const double wf0 = b2c_clip(0.0, lb0, ub0), wf1 = b2c_clip(0.0, lb1, ub1);
+        const double wo0 = fresh ? wf0 : ws0;
+        const double wo1 = fresh ? wf1 : ws1;
 #ifdef __CUDA_ARCH__
         if (team) __syncwarp();                       // every lane has read stage k of the strips it borrows
 #endif
-        double w0 = wo0, w1 = wo1;
-        if (gain) {
+        double w0, w1;
+        {
+            // closed-loop update, computed by every lane (u is zero / stale where it does not count) and selected
             const double dx = zx - ox, dy = zy - oy, dth = zt - ot;
-            w0 = wo0 - alpha * u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
-            w1 = wo1 - alpha * u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
+            double c0 = wo0 - alpha * u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
+            double c1 = wo1 - alpha * u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
             if (any_arc) {
                 if (arc) {
                     const double d0 = -u[6] - (u[0] * ldx + u[1] * ldy + u[2] * ldth);
                     const double d1 = -u[7] - (u[3] * ldx + u[4] * ldy + u[5] * ldth);
-                    w0 = wo0 + alpha * d0;
-                    w1 = wo1 + alpha * d1;
+                    c0 = wo0 + alpha * d0;
+                    c1 = wo1 + alpha * d1;
                     const double vra = b2c_guard_v(uo0, B2C_GUARD_MPC);
                     const double nldx = ldx + (-vra * sk) * ldth + ck * d0;
                     const double nldy = ldy + (vra * ck) * ldth + sk * d0;
                     ldth = ldth + a.dt * d1; ldx = nldx; ldy = nldy;
                 }
             }
-            w0 = b2c_clip(w0, lb0, ub0);
-            w1 = b2c_clip(w1, lb1, ub1);
+            c0 = b2c_clip(c0, lb0, ub0);
+            c1 = b2c_clip(c1, lb1, ub1);
+            w0 = gain ? c0 : wo0;
+            w1 = gain ? c1 : wo1;
         }
         if (gain || fresh) { MW(2 * k) = w0; MW(2 * k + 1) = w1; }
         if (gain && act) gw_store(m, k, wo0, wo1);            // what the trial replaces: kept for the undo
