@@ -373,7 +373,9 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
             w1 = gain ? c1 : wo1;
         }
         if (gain || fresh) { MW(2 * k) = w0; MW(2 * k + 1) = w1; }
-        if (gain && act) gw_store(m, k, wo0, wo1);            // what the trial replaces: kept for the undo
+        // what a trial replaces, kept for the undo.  Unconditional (no branch region in the stage): GW is only read
+        // after a gain sweep of its own lane, which has rewritten it; other lanes store values nobody reads
+        gw_store(m, k, wo0, wo1);
         double wxx = a.q0, wxy = 0.0, wyy = a.q1;
         double gx = a.q0 * zx, gy = a.q1 * zy;
         const double gt = a.q2 * zt;
