@@ -63,3 +63,30 @@ def test_reference_run_simulation_mpc_mode_unmodified(golden, tmp_path):
     ms = np.array([float(r["solve_time_ms"]) for r in ct])
     assert np.median(ms) < 5.0                                                 # shipped log: 82.6 ms mean
     assert re.search(r"Collision events: \d+", out) and "Mean MPC solve time" in out
+
+
+def test_reference_run_simulation_hybrid_mode_unmodified(tmp_path):
+    """`--mode hybrid` (run_hybrid_simulation :413-638): the reference's own loop drives the drop-in LQRController,
+    MPCController (block_size 1, every tick) and RiskMetrics mirror, one scalar call per tick.  The reference ships no
+    log of this mode with its final parameters, so the run is compared with the DEVICE rollout engine executing the same
+    loop for the same robot (b2c_rollout_host, hybrid mode): identical controller choice at every tick, states to 1e-9."""
+    import re as _re
+    from hybrid_controller.rollout import simulate_batch
+    from hybrid_controller.controllers import LQRController, MPCController, RiskMetrics
+    from hybrid_controller import workloads as wl
+    out, st, ct = _run("hybrid", tmp_path)
+    x = np.array([[float(r[k]) for k in ("px", "py", "theta")] for r in st])
+    u = np.array([[float(r[k]) for k in ("v", "omega")] for r in ct])
+    tags = np.array([1 if r["controller"] == "MPC" else 0 for r in ct])
+    assert x.shape == (999, 3) and 0 < tags.sum() < 999
+    m = _re.search(r"LQR steps: (\d+).*\n\s*MPC steps: (\d+).*\n\s*Controller switches: (\d+)", out)
+    assert m and int(m.group(1)) + int(m.group(2)) == 999
+    table = wl.figure8_table()
+    ref = simulate_batch("hybrid", table, [0], table[0:1, 1:4], wl.DEFAULT_OBSTACLES, 999, lqr=LQRController(**wl.SIM_LQR),
+                         mpc=MPCController(horizon=6, block_size=1, **wl.SIM_MPC),
+                         risk=RiskMetrics(d_safe=0.3, d_trigger=1.0, alpha=0.6, beta=0.4, threshold_low=0.2,
+                                          threshold_medium=0.5), log=True)
+    assert np.array_equal(ref["controller"][0], tags)
+    assert int(m.group(1)) == ref["lqr_steps"][0] and int(m.group(2)) == ref["mpc_solves"][0]
+    assert int(m.group(3)) == ref["switches"][0]
+    assert np.abs(ref["states"][0][:999] - x).max() <= 1e-9 and np.abs(ref["controls"][0] - u).max() <= 1e-9
