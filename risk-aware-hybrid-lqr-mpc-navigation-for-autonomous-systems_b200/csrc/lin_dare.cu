@@ -154,11 +154,27 @@ B2C_HD M3 m3_inv(const M3& a) {
     r.m[8] = fma(a.m[0], a.m[4], -a.m[1] * a.m[3]) * id;
     return r;
 }
-B2C_HD void m3_symmetrize(M3& a) {
-    double t;
-    t = 0.5 * (a.m[1] + a.m[3]); a.m[1] = t; a.m[3] = t;
-    t = 0.5 * (a.m[2] + a.m[6]); a.m[2] = t; a.m[6] = t;
-    t = 0.5 * (a.m[5] + a.m[7]); a.m[5] = t; a.m[7] = t;
+// products whose result is symmetric in exact arithmetic: the six upper entries are computed, the lower ones mirrored
+#define M3_MIRROR(r) do { (r).m[3] = (r).m[1]; (r).m[6] = (r).m[2]; (r).m[7] = (r).m[5]; } while (0)
+B2C_HD M3 m3_mul_sym(const M3& a, const M3& b) {
+    M3 r;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = i; j < 3; j++)
+            r.m[i * 3 + j] = fma(a.m[i * 3 + 2], b.m[6 + j], fma(a.m[i * 3 + 1], b.m[3 + j], a.m[i * 3] * b.m[j]));
+    M3_MIRROR(r);
+    return r;
+}
+B2C_HD M3 m3_mul_tn_sym(const M3& a, const M3& b) {   // a' b
+    M3 r;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = i; j < 3; j++)
+            r.m[i * 3 + j] = fma(a.m[6 + i], b.m[6 + j], fma(a.m[3 + i], b.m[3 + j], a.m[i] * b.m[j]));
+    M3_MIRROR(r);
+    return r;
 }
 
 #define DARE_MAX_ITER 33   // 2^33 steps: closed-loop |lambda| up to 1-1e-9; beyond that "no finite solution"
@@ -189,22 +205,23 @@ B2C_HD void dare_solve_one(int64_t i, int64_t B, int method, int guard, double d
         W.m[0] += 1.0; W.m[4] += 1.0; W.m[8] += 1.0;
         M3 Wi = m3_inv(W);
         M3 T = m3_mul(A, Wi);                 // A W^-1
-        M3 HW = m3_mul(H, Wi);                // H W^-1 (symmetric in exact arithmetic)
-        M3 Hn = m3_mul_tn(A, m3_mul(HW, A));  // A' H W^-1 A
-        M3 Gn = m3_mul(T, m3_mul_nt(G, A));   // A W^-1 G A'
+        M3 HW = m3_mul_sym(H, Wi);                // H W^-1 = (I + H G)^-1 H: symmetric
+        M3 Hn = m3_mul_tn_sym(A, m3_mul(HW, A));  // A' H W^-1 A: symmetric
+        M3 Gn = m3_mul_sym(T, m3_mul_nt(G, A));   // A W^-1 G A': symmetric
         A = m3_mul(T, A);
         double dmax = 0.0, hmax = 0.0;
 #pragma unroll
-        for (int e = 0; e < 9; e++) { Gn.m[e] += G.m[e]; }
-        m3_symmetrize(Hn);
-#pragma unroll
         for (int e = 0; e < 9; e++) {
-            dmax = fmax(dmax, fabs(Hn.m[e]));
+            G.m[e] += Gn.m[e];
             H.m[e] += Hn.m[e];
-            hmax = fmax(hmax, fabs(H.m[e]));
         }
-        m3_symmetrize(Gn);
-        G = Gn;
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = i; j < 3; j++) {
+                dmax = fmax(dmax, fabs(Hn.m[i * 3 + j]));
+                hmax = fmax(hmax, fabs(H.m[i * 3 + j]));
+            }
         if (!(hmax < 1e300)) { st = B2C_NONFINITE; break; }   // catches NaN and overflow
         if (dmax <= 1e-15 * hmax) {
             // A_k = (closed loop)^(2^k) must have died out; if it has not, the pencil has an
