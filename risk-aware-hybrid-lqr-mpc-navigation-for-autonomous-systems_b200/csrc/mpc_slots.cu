@@ -42,6 +42,7 @@ struct SlotMem {
     double* gg; int64_t gs;                           // mirror strip of this slot: gains of stage j at gg + j*8*gs
     double* gw;                                       // the inputs a trial replaced: stage j at gw + j*2*gs
     uint32_t tm;                                      // TMEM address of this warp's U block (stage k at tm + 16k)
+    uint32_t tmg; bool mir;                           // mir: the gains mirror GG lives in tensor memory (stage j at tmg + 16j)
 };
 struct Stage6 { double ck, sk, uo0, uo1, prx, pry; };
 B2C_HD Stage6 g_load(const SlotMem& m, int k) {
@@ -281,14 +282,32 @@ B2C_HD void slot_row(const MpcArgs& a, double ddx, double ddy, double d2, double
                      double& J, double& mv, double& gx, double& gy, double& wxx, double& wxy, double& wyy) {
     const double inv = B2C_RSQRT(d2);
     const double nx = ddx * inv, ny = ddy * inv;
-    const double viol = c - (d2 * inv + nx * zx + ny * zy);
+    const double viol = c - fma(nx, zx, fma(ny, zy, d2 * inv));
     if (viol > 0.0) {
         mv = fmax(mv, viol);
-        J += a.rho * viol * viol;
+        J = fma(a.rho * viol, viol, J);
         const double rn0 = a.rho * nx, rn1 = a.rho * ny;
-        wxx += rn0 * nx; wxy += rn0 * ny; wyy += rn1 * ny;
-        gx -= rn0 * viol; gy -= rn1 * viol;
+        wxx = fma(rn0, nx, wxx); wxy = fma(rn0, ny, wxy); wyy = fma(rn1, ny, wyy);
+        gx = fma(-rn0, viol, gx); gy = fma(-rn1, viol, gy);
     }
+}
+
+// the same row with selects instead of a branch (`on`-less lanes keep every accumulator): the first violated row of a
+// stage is evaluated by every lane of the warp in straight-line code -- some lane of a warp has one in four stages
+// out of five, and a divergent region per stage costs a lone warp more than the arithmetic does
+B2C_HD void slot_row_sel(const MpcArgs& a, const bool has, double ddx, double ddy, double d2, double c, double zx, double zy,
+                         double& J, double& mv, double& gx, double& gy, double& wxx, double& wxy, double& wyy) {
+    const double inv = B2C_RSQRT(d2);
+    const double nx = ddx * inv, ny = ddy * inv;
+    const double viol = c - fma(nx, zx, fma(ny, zy, d2 * inv));
+    const bool on = has && (viol > 0.0);
+    const double rn0 = a.rho * nx, rn1 = a.rho * ny;
+    const double mv1 = fmax(mv, viol), J1 = fma(a.rho * viol, viol, J);
+    const double wxx1 = fma(rn0, nx, wxx), wxy1 = fma(rn0, ny, wxy), wyy1 = fma(rn1, ny, wyy);
+    const double gx1 = fma(-rn0, viol, gx), gy1 = fma(-rn1, viol, gy);
+    mv = on ? mv1 : mv; J = on ? J1 : J;
+    wxx = on ? wxx1 : wxx; wxy = on ? wxy1 : wxy; wyy = on ? wyy1 : wyy;
+    gx = on ? gx1 : gx; gy = on ? gy1 : gy;
 }
 
 // ----- forward sweep -------------------------------------------------------------------------------
@@ -339,10 +358,10 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         ring_issue<SS>(m, k + 2, act && k + 2 < N, ck + pry);       // constants two stages ahead
         double u[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         if (any_gain) u_load8<SS, KT>(m, k, u, dU, srcU, team);       // the gains of this stage (any_gain: warp-uniform)
+        const double ws0 = wsrc[(2 * k) * SS], ws1 = wsrc[(2 * k + 1) * SS];
         const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
         // selects, not branches: the common path of a stage stays one basic block (a lone warp on its scheduler lives
         // off the instruction-level parallelism the compiler finds inside it)
-        const double ws0 = wsrc[(2 * k) * SS], ws1 = wsrc[(2 * k + 1) * SS];
         const double wf0 = b2c_clip(0.0, lb0, ub0), wf1 = b2c_clip(0.0, lb1, ub1);
         const double wo0 = fresh ? wf0 : ws0;
         const double wo1 = fresh ? wf1 : ws1;
@@ -353,18 +372,18 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         {
             // closed-loop update, computed by every lane (u is zero / stale where it does not count) and selected
             const double dx = zx - ox, dy = zy - oy, dth = zt - ot;
-            double c0 = wo0 - alpha * u[6] - (u[0] * dx + u[1] * dy + u[2] * dth);
-            double c1 = wo1 - alpha * u[7] - (u[3] * dx + u[4] * dy + u[5] * dth);
+            double c0 = fma(-u[2], dth, fma(-alpha, u[6], wo0)) - fma(u[0], dx, u[1] * dy);
+            double c1 = fma(-u[5], dth, fma(-alpha, u[7], wo1)) - fma(u[3], dx, u[4] * dy);
             if (any_arc) {
                 if (arc) {
-                    const double d0 = -u[6] - (u[0] * ldx + u[1] * ldy + u[2] * ldth);
-                    const double d1 = -u[7] - (u[3] * ldx + u[4] * ldy + u[5] * ldth);
-                    c0 = wo0 + alpha * d0;
-                    c1 = wo1 + alpha * d1;
+                    const double d0 = -fma(u[0], ldx, fma(u[1], ldy, fma(u[2], ldth, u[6])));
+                    const double d1 = -fma(u[3], ldx, fma(u[4], ldy, fma(u[5], ldth, u[7])));
+                    c0 = fma(alpha, d0, wo0);
+                    c1 = fma(alpha, d1, wo1);
                     const double vra = b2c_guard_v(uo0, B2C_GUARD_MPC);
-                    const double nldx = ldx + (-vra * sk) * ldth + ck * d0;
-                    const double nldy = ldy + (vra * ck) * ldth + sk * d0;
-                    ldth = ldth + a.dt * d1; ldx = nldx; ldy = nldy;
+                    const double nldx = fma(ck, d0, fma(-vra * sk, ldth, ldx));
+                    const double nldy = fma(sk, d0, fma(vra * ck, ldth, ldy));
+                    ldth = fma(a.dt, d1, ldth); ldx = nldx; ldy = nldy;
                 }
             }
             c0 = b2c_clip(c0, lb0, ub0);
@@ -379,18 +398,23 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
         double wxx = a.q0, wxy = 0.0, wyy = a.q1;
         double gx = a.q0 * zx, gy = a.q1 * zy;
         const double gt = a.q2 * zt;
-        J += a.q0 * zx * zx + a.q1 * zy * zy + a.q2 * zt * zt;
+        J = fma(gx, zx, fma(gy, zy, fma(gt, zt, J)));
         if (MT > 0) {
             unsigned hit = 0;
+            double cdx = 1.0, cdy = 0.0, cd2 = 1.0, cc = 0.0;       // the lowest violated row (harmless values if none)
 #pragma unroll
-            for (int mm = 0; mm < MR; ++mm) {
+            for (int mm = MR - 1; mm >= 0; --mm) {
                 const double ddx = prx - OX[mm], ddy = pry - OY[mm];
                 const double d2 = ddx * ddx + ddy * ddy;
-                const double q = d2 + ddx * zx + ddy * zy;
-                if ((d2 > 1e-4) && (OCC[mm] * d2 > q * fabs(q))) hit |= (1u << mm);
+                const double q = fma(ddx, zx, fma(ddy, zy, d2));
+                const bool h = (d2 > 1e-4) && (OCC[mm] * d2 > q * fabs(q));
+                if (h) hit |= (1u << mm);
+                cdx = h ? ddx : cdx; cdy = h ? ddy : cdy; cd2 = h ? d2 : cd2; cc = h ? OC[mm] : cc;
             }
             if (!act) hit = 0;
-            while (hit) {                                 // rare; lanes with different rows share an iteration
+            slot_row_sel(a, hit != 0u, cdx, cdy, cd2, cc, zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
+            hit &= hit - 1u;
+            while (hit) {                                 // a second violated row in one stage: rare
 #ifdef __CUDA_ARCH__
                 const int mm = __ffs(hit) - 1;
 #else
@@ -404,27 +428,27 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
             for (int mm = 0; mm < M; ++mm) {
                 const double ddx = prx - osrc[(3 * mm) * SS], ddy = pry - osrc[(3 * mm + 1) * SS], c = osrc[(3 * mm + 2) * SS];
                 const double d2 = ddx * ddx + ddy * ddy;
-                const double q = d2 + ddx * zx + ddy * zy;
+                const double q = fma(ddx, zx, fma(ddy, zy, d2));
                 if (act && (d2 > 1e-4) && (c * fabs(c) * d2 > q * fabs(q)))
                     slot_row(a, ddx, ddy, d2, c, zx, zy, J, mv, gx, gy, wxx, wxy, wyy);
             }
         }
         const double ut0 = w0 + uo0, ut1 = w1 + uo1;
-        J += a.r0 * ut0 * ut0 + a.r1 * ut1 * ut1;
+        J = fma(a.r0 * ut0, ut0, fma(a.r1 * ut1, ut1, J));
         u[0] = gx;  u[1] = gy;  u[2] = gt;
         u[3] = wxx; u[4] = wxy; u[5] = wyy;
         u[6] = 0.0; u[7] = 0.0;
         u_store8<SS, KT>(m, k, u);
         const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);                       // :425
         const double a_k = -vr * sk, b_k = vr * ck;
-        const double nzx = zx + a_k * zt + ck * w0, nzy = zy + b_k * zt + sk * w0;
-        const double nox = ox + a_k * ot + ck * wo0, noy = oy + b_k * ot + sk * wo0;
-        zt = zt + a.dt * w1; zx = nzx; zy = nzy;
-        ot = ot + a.dt * wo1; ox = nox; oy = noy;
+        const double nzx = fma(ck, w0, fma(a_k, zt, zx)), nzy = fma(sk, w0, fma(b_k, zt, zy));
+        const double nox = fma(ck, wo0, fma(a_k, ot, ox)), noy = fma(sk, wo0, fma(b_k, ot, oy));
+        zt = fma(a.dt, w1, zt); zx = nzx; zy = nzy;
+        ot = fma(a.dt, wo1, ot); ox = nox; oy = noy;
     }
     u_fence<KT>();
-    J += a.p0 * zx * zx + a.p1 * zy * zy + a.p2 * zt * zt;                       // terminal cost, :412
     lamx = a.p0 * zx; lamy = a.p1 * zy; lamt = a.p2 * zt;
+    J = fma(lamx, zx, fma(lamy, zy, fma(lamt, zt, J)));                          // terminal cost, :412
     max_viol = mv;
     return J;
 }
@@ -444,75 +468,91 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     // the mirror store of stage j+1 is issued one stage late, from registers nothing else wants in between
     // (issued in place, the next writes to its source registers stalled on the store queue)
     double pm[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#if defined(__CUDA_ARCH__)
+    const bool mir = (KT == 0) && m.mir;              // warp-uniform
+#else
+    const bool mir = false;
+#endif
     ringb_issue<SS>(m, N - 1, 0, act, 0.0);
     ringb_issue<SS>(m, N - 2, 1, act && N > 1, 0.0);
     ringb_issue<SS>(m, N - 3, 2, act && N > 2, 0.0);
     int rs = 0;                                       // ring slot of stage j
     for (int j = N - 1; j >= 0; --j) {
-        if (act && j < N - 1) gg_store(m, j + 1, pm);
+        if (!mir && act && j < N - 1) gg_store(m, j + 1, pm);
         double ck, sk, uo0, uo1;
         ringb_take<SS>(m, j, rs, ck, sk, uo0, uo1);
         ringb_issue<SS>(m, j - 3, rs, act && j >= 3, ck + uo1);     // constants three stages ahead, into the cell just read
         rs = (rs == 2) ? 0 : rs + 1;
-        double u[8];
-        u_load8<SS, KT>(m, j, u);
-        const double gz0 = u[0], gz1 = u[1], gz2 = u[2];
-        const double H0 = u[3], H1 = u[4], H3 = u[5];
+        double u[8], uold[8];
+        u_load8<SS, KT>(m, j, uold);
+        const double gz0 = uold[0], gz1 = uold[1], gz2 = uold[2];
+        const double H0 = uold[3], H1 = uold[4], H3 = uold[5];
         const double w0 = MW(2 * j), w1 = MW(2 * j + 1);
         const double gu0 = a.r0 * (w0 + uo0), gu1 = a.r1 * (w1 + uo1);
         const double vr = b2c_guard_v(uo0, B2C_GUARD_MPC);
         const double al = -vr * sk, be = vr * ck;
         // true gradient wrt w_j decides which bounded inputs are frozen; then the costate update
-        const double gt0 = gu0 + ck * l0 + sk * l1;
-        const double gt1 = gu1 + dt * l2;
+        // (sums of products are written as nested fma: one rounding and one 8-cycle step per term, and the
+        // compiler may not re-associate them itself)
+        const double gt0 = fma(ck, l0, fma(sk, l1, gu0));
+        const double gt1 = fma(dt, l2, gu1);
         {
-            const double nl2 = gz2 + al * l0 + be * l1 + l2;
+            const double nl2 = fma(al, l0, fma(be, l1, gz2 + l2));
             l0 = gz0 + l0; l1 = gz1 + l1; l2 = nl2;
         }
         const double lb0 = -a.v_max - uo0, ub0 = a.v_max - uo0, lb1 = -a.w_max - uo1, ub1 = a.w_max - uo1;
         const bool c0 = (w0 <= lb0 && gt0 > 0.0) || (w0 >= ub0 && gt0 < 0.0);
         const bool c1 = (w1 <= lb1 && gt1 > 0.0) || (w1 >= ub1 && gt1 < 0.0);
         // third column of S*A
-        const double t0 = al * s00 + be * s01 + s02;
-        const double t1 = al * s01 + be * s11 + s12;
-        const double t2 = al * s02 + be * s12 + s22;
+        const double t0 = fma(al, s00, fma(be, s01, s02));
+        const double t1 = fma(al, s01, fma(be, s11, s12));
+        const double t2 = fma(al, s02, fma(be, s12, s22));
         const double Q00 = H0 + s00, Q01 = H1 + s01, Q02 = t0;
         const double Q11 = H3 + s11, Q12 = t1;
-        const double Q22 = a.q2 + al * t0 + be * t1 + t2;
-        double U00 = ck * s00 + sk * s01, U01 = ck * s01 + sk * s11, U02 = ck * t0 + sk * t1;
+        const double Q22 = fma(al, t0, fma(be, t1, a.q2 + t2));
+        double U00 = fma(ck, s00, sk * s01), U01 = fma(ck, s01, sk * s11), U02 = fma(ck, t0, sk * t1);
         double U10 = dt * s02, U11 = dt * s12, U12 = dt * t2;
-        double R00 = a.r0 + ck * U00 + sk * U01;
-        double R01 = ck * U10 + sk * U11;
-        double R11 = a.r1 + dt * dt * s22;
-        const double qz0 = gz0 + v0, qz1 = gz1 + v1, qz2 = gz2 + al * v0 + be * v1 + v2;
-        double qu0 = gu0 + ck * v0 + sk * v1;
-        double qu1 = gu1 + dt * v2;
+        double R00 = fma(ck, U00, fma(sk, U01, a.r0));
+        double R01 = fma(ck, U10, sk * U11);
+        double R11 = fma(dt * dt, s22, a.r1);
+        const double qz0 = gz0 + v0, qz1 = gz1 + v1, qz2 = fma(al, v0, fma(be, v1, gz2 + v2));
+        double qu0 = fma(ck, v0, fma(sk, v1, gu0));
+        double qu1 = fma(dt, v2, gu1);
         // frozen inputs: selects, not branches (lanes of a warp freeze different inputs at every stage)
         R00 = c0 ? 1.0 : R00; U00 = c0 ? 0.0 : U00; U01 = c0 ? 0.0 : U01; U02 = c0 ? 0.0 : U02; qu0 = c0 ? 0.0 : qu0;
         R11 = c1 ? 1.0 : R11; U10 = c1 ? 0.0 : U10; U11 = c1 ? 0.0 : U11; U12 = c1 ? 0.0 : U12; qu1 = c1 ? 0.0 : qu1;
         R01 = (c0 || c1) ? 0.0 : R01;
-        const double idet = B2C_RCP(R00 * R11 - R01 * R01);
+        const double idet = B2C_RCP(fma(R00, R11, -(R01 * R01)));
         const double i00 = R11 * idet, i01 = -R01 * idet, i11 = R00 * idet;
-        const double K00 = i00 * U00 + i01 * U10, K01 = i00 * U01 + i01 * U11, K02 = i00 * U02 + i01 * U12;
-        const double K10 = i01 * U00 + i11 * U10, K11 = i01 * U01 + i11 * U11, K12 = i01 * U02 + i11 * U12;
-        const double k0 = i00 * qu0 + i01 * qu1, k1 = i01 * qu0 + i11 * qu1;
-        u[0] = K00; u[1] = K01; u[2] = K02; u[3] = K10; u[4] = K11; u[5] = K12; u[6] = k0; u[7] = k1;
+        const double K00 = fma(i00, U00, i01 * U10), K01 = fma(i00, U01, i01 * U11), K02 = fma(i00, U02, i01 * U12);
+        const double K10 = fma(i01, U00, i11 * U10), K11 = fma(i01, U01, i11 * U11), K12 = fma(i01, U02, i11 * U12);
+        const double k0 = fma(i00, qu0, i01 * qu1), k1 = fma(i01, qu0, i11 * qu1);
+        // a lane without a sweep of its own puts back what it read: its strip may hold the gains a rejected trial has
+        // just been given back (the undo runs before this phase)
+        u[0] = act ? K00 : uold[0]; u[1] = act ? K01 : uold[1]; u[2] = act ? K02 : uold[2]; u[3] = act ? K10 : uold[3];
+        u[4] = act ? K11 : uold[4]; u[5] = act ? K12 : uold[5]; u[6] = act ? k0 : uold[6];  u[7] = act ? k1 : uold[7];
         u_store8<SS, KT>(m, j, u);
+#if defined(__CUDA_ARCH__)
+        if (mir) tm_st16(m.tmg + 16u * (uint32_t)j, u);   // the mirror: one warp-wide store (idempotent for the other lanes)
+#endif
 #pragma unroll
         for (int e = 0; e < 8; ++e) pm[e] = u[e];
-        dec += 0.5 * (qu0 * k0 + qu1 * k1);
-        s00 = Q00 - (U00 * K00 + U10 * K10);
-        s01 = Q01 - (U00 * K01 + U10 * K11);
-        s02 = Q02 - (U00 * K02 + U10 * K12);
-        s11 = Q11 - (U01 * K01 + U11 * K11);
-        s12 = Q12 - (U01 * K02 + U11 * K12);
-        s22 = Q22 - (U02 * K02 + U12 * K12);
-        v0 = qz0 - (U00 * k0 + U10 * k1);
-        v1 = qz1 - (U01 * k0 + U11 * k1);
-        v2 = qz2 - (U02 * k0 + U12 * k1);
+        dec = fma(0.5, fma(qu0, k0, qu1 * k1), dec);
+        s00 = fma(-U00, K00, fma(-U10, K10, Q00));
+        s01 = fma(-U00, K01, fma(-U10, K11, Q01));
+        s02 = fma(-U00, K02, fma(-U10, K12, Q02));
+        s11 = fma(-U01, K01, fma(-U11, K11, Q11));
+        s12 = fma(-U01, K02, fma(-U11, K12, Q12));
+        s22 = fma(-U02, K02, fma(-U12, K12, Q22));
+        v0 = fma(-U00, k0, fma(-U10, k1, qz0));
+        v1 = fma(-U01, k0, fma(-U11, k1, qz1));
+        v2 = fma(-U02, k0, fma(-U12, k1, qz2));
     }
-    if (act) gg_store(m, 0, pm);
+    if (!mir && act) gg_store(m, 0, pm);
     u_fence<KT>();
+#if defined(__CUDA_ARCH__)
+    if (mir) tm_fence_st();
+#endif
     return dec;
 }
 
@@ -525,6 +565,33 @@ template <int SS, int KT>
 B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred) {
     const int N = a.N;
     constexpr int C = 4;
+#if defined(__CUDA_ARCH__)
+    if (KT == 0 && m.mir) {
+        // gains from the mirror in tensor memory (every lane loads, `pred` lanes store to their strip), inputs from GW
+        for (int j0 = 0; j0 < N; j0 += C) {
+            double2 wp[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const int j = (j0 + c < N) ? (j0 + c) : (N - 1);
+                wp[c] = make_double2(0.0, 0.0);
+                if (pred) wp[c] = *reinterpret_cast<const double2*>(m.gw + (int64_t)j * 2 * m.gs);
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const int j = j0 + c;
+                if (j < N) {
+                    double u[8];
+                    tm_ld16(m.tmg + 16u * (uint32_t)j, u);
+                    if (pred) {
+                        MW(2 * j) = wp[c].x; MW(2 * j + 1) = wp[c].y;
+                        u_store8<SS, KT>(m, j, u);
+                    }
+                }
+            }
+        }
+        return;
+    }
+#endif
     for (int j0 = 0; j0 < N; j0 += C) {
         double2 wp[C], q0[C], q1[C], q2[C], q3[C];
 #pragma unroll
@@ -777,12 +844,16 @@ k_mpc_slots(const MpcArgs a) {
     m.gg = a.scratch + ((int64_t)blockIdx.x * tpb + threadIdx.x) * 8;
     m.gw = a.scratch + (int64_t)8 * a.N * a.nslots + ((int64_t)blockIdx.x * tpb + threadIdx.x) * 2;
     m.g = nullptr; m.gst = 6 * 32;
-    m.tm = 0;
+    m.tm = 0; m.tmg = 0;
+    m.mir = (KT == 0) && (a.mir != 0);
     uint32_t tmb = 0;
-    if (KT > 0) {
+    if (KT > 0 || m.mir) {
         // all 512 columns of this SM's tensor memory: warps 0-3 use columns [0, 16 KT), warps 4-7 [16 KT, 32 KT); each
-        // warp addresses its own lane quadrant (warp % 4), each thread its own lane: 16 columns = one stage of U
-        volatile uint32_t* tm_base_p = reinterpret_cast<volatile uint32_t*>(smem + (size_t)(nfields + 12) * tpb);
+        // warp addresses its own lane quadrant (warp % 4), each thread its own lane: 16 columns = one stage of U.
+        // KT == 0 with a.mir: the same columns hold the gains MIRROR (N stages per warp) instead of U itself.
+        // The allocator's answer goes through shared memory: the spare word behind the strips (KT > 0), or the first
+        // word of the ring memory, which nothing uses before the loop (KT == 0: the strips fill shared memory)
+        volatile uint32_t* tm_base_p = reinterpret_cast<volatile uint32_t*>(smem + (size_t)(nfields + (KT > 0 ? 12 : 0)) * tpb);
         if (warp == 0) {
             const uint32_t dst = (uint32_t)__cvta_generic_to_shared((const void*)tm_base_p);
             asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(dst), "r"(512u) : "memory");
@@ -793,6 +864,8 @@ k_mpc_slots(const MpcArgs a) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         tmb = *tm_base_p;
         m.tm = tmb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * (16 * KT));
+        m.tmg = tmb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * (16 * a.N));
+        if (KT == 0) __syncthreads();                         // everyone has the address before the ring is used
     }
     SlotState s;
     s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0; s.rej = 0; s.undo = 0;
@@ -806,6 +879,17 @@ k_mpc_slots(const MpcArgs a) {
           long long tr_undo = 0, tr_team = 0, tr_sweep = 0, tr_post = 0, tr_teamrounds = 0, tr_c2 = 0, tr_tb = 0, tr_tf = 0, tr_bact = 0;)
     for (;;) {
         TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE));)
+        // ---- rejected trials are undone first (inputs from GW, gains from the mirror): the backward phase leaves the
+        // strips of lanes without a sweep as they are, and with the mirror in tensor memory it rewrites every lane's
+        // mirror from its strip, so strip and mirror must agree by then
+        {
+            const bool und = (s.undo != 0);
+            if (__any_sync(FULL, und)) {
+                slot_undo<SS, KT>(a, m, und);
+                s.undo = 0;
+            }
+        }
+        TRACE(__syncwarp(); tr_undo += clock64() - tr_c;)
         // ---- backward phase -----------------------------------------------------------------------------
         {
             const bool act = (s.mode == SLOT_BWD);
@@ -870,16 +954,8 @@ k_mpc_slots(const MpcArgs a) {
         if (empty && __all_sync(FULL, s.mode == SLOT_IDLE)) break;
         __syncwarp();
         TRACE(tr_r += clock64() - tr_c; tr_c = clock64();)
-        // ---- forward phase: rejected trials are undone, then every lane with a sweep to run, plus the idle lanes lent
-        // to requesting instances
-        {
-            const bool und = (s.undo != 0);
-            if (__any_sync(FULL, und)) {
-                slot_undo<SS, KT>(a, m, und);
-                s.undo = 0;
-            }
-        }
-        TRACE(__syncwarp(); tr_undo += clock64() - tr_c; tr_c2 = clock64();)
+        // ---- forward phase: every lane with a sweep to run, plus the idle lanes lent to requesting instances
+        TRACE(tr_c2 = clock64();)
         const bool gain = (s.mode == SLOT_FWD_GAIN);
         const unsigned idle_m = __ballot_sync(FULL, s.mode == SLOT_IDLE);
         const bool team_round = (idle_m != 0u) && (req_m != 0u);          // warp-uniform
@@ -973,7 +1049,7 @@ k_mpc_slots(const MpcArgs a) {
             t[8] = tr_undo; t[9] = tr_team; t[10] = tr_sweep; t[11] = tr_post; t[12] = tr_teamrounds; t[13] = tr_tf; t[14] = tr_bact;
         }
     })
-    if (KT > 0) {
+    if (KT > 0 || m.mir) {
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmb), "r"(512u) : "memory");
@@ -1078,7 +1154,10 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int) {
     // a kernel that allocates all of an SM's tensor memory must be alone on that SM (a second CTA would wait for
     // columns until the first exits): ask for more than half of the shared memory
     size_t smem = c.smem;
-    if (c.kt > 0 && smem < 120 * 1024) smem = 120 * 1024;
+    // the gains mirror goes to tensor memory when U is in shared memory and N stages per warp fit the 512 columns
+    a.mir = (c.kt == 0 && ((c.tpb + 127) / 128) * 16 * a.N <= 512) ? 1 : 0;
+    if (const char* e = getenv("B2C_SLOTS_MIRROR")) a.mir = (a.mir && atoi(e) != 0) ? 1 : 0;   // developer switch (A/B runs)
+    if ((c.kt > 0 || a.mir) && smem < 120 * 1024) smem = 120 * 1024;
     // more than one instance per slot: claim in difficulty order (see mpc_class_of)
     const bool ordered = slot_ordered(a, a.nslots);
     size_t strips, recs, perm;
