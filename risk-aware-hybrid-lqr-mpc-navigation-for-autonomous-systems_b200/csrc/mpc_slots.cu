@@ -205,20 +205,28 @@ struct SlotState {
     double alpha, J, dec, z0x, z0y, z0t, lamx, lamy, lamt, max_viol;
     int rej;                                          // a trial step of this solve has been rejected (kernel: asks for helper lanes)
     int undo;                                         // a rejected trial is still to be undone (inputs and gains from the mirrors)
+#ifdef B2C_SLOT_TRACE
+    int rounds, round0;                               // trace build: rounds this instance was resident, warp round it was claimed in
+#endif
 };
 
 // ----- difficulty classes (work ordering only; never changes a result) ------------------------------
 // The Newton iteration count of an instance is predicted well by how deep its REFERENCE path runs into
 // an inflated obstacle: margin = min_{k<N, m} (|p_ref,k - p_obs,m| - (d_safe + r_m)).  On config 4:
-// margin < -0.1 m -> 4.7 iterations on average (max 13), [-0.1, 0) -> 2.9, [0, 0.1) -> 1.7, >= 0.1 -> 1.26
-// (max 5).  The persistent kernel claims the hard classes first (longest-processing-time-first), which
-// removes the tail a first-come queue leaves when the last instances claimed happen to be slow ones, and
-// keeps warps homogeneous (lanes of a warp finish, and refill, together).
-#define MPC_NCLASS 4
+// margin < -0.1 m -> 4.7 iterations on average (max 13), [-0.1, 0) -> 2.9, [0, 0.1) -> 1.7, [0.1, 0.2) -> 1.27
+// (max 5), >= 0.2 -> 1.25 (max 2).  The persistent kernel claims the hard classes first (longest-processing-time-
+// first): what decides the makespan of a batch that fills the slots only a few times is what the LAST claims are --
+// the per-instance trace of config 4 showed instances of 3-5 iterations claimed in round 13-14 of 19 finishing last.
+// So the easy end is split further: margin >= 0.2 with a large initial heading error (one more iteration in 55 % of
+// the cases above 0.15 rad, the turn rate saturates) before margin >= 0.2 with a small one (5-9 % below 0.1 rad),
+// which is claimed last: two rounds each, almost surely.  Classes also keep warps homogeneous (lanes of a warp finish,
+// and refill, together).
+#define MPC_NCLASS 6
+#define MPC_MARGIN_CLASSES 5
 B2C_HD int mpc_class_of(double d2, double c) {
-    const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1;
-    const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp);
-    return (d2 < t0) ? 0 : (d2 < t1) ? 1 : (d2 < t2) ? 2 : 3;
+    const double cm = fmax(c - 0.1, 0.0), cp = c + 0.1, cq = c + 0.2;
+    const double t0 = cm * cm, t1 = c * fabs(c), t2 = cp * fabs(cp), t3 = cq * fabs(cq);
+    return (d2 < t0) ? 0 : (d2 < t1) ? 1 : (d2 < t2) ? 2 : (d2 < t3) ? 3 : 4;
 }
 
 // ----- prepared record of instance i (:392-401 unwrap + branch shift, :421 error state, :424-428 linearization inputs)
@@ -245,7 +253,7 @@ B2C_HD int prep_instance(const MpcArgs& a, int64_t i, double* g, int64_t gst, do
             hdr[6 + 3 * e] = a.d_safe + mpc_in_obs(a, i, 3 * e + 2);
         }
     }
-    int cls = MPC_NCLASS - 1;
+    int cls = MPC_MARGIN_CLASSES - 1;
     double th_prev = r0t, cum = 0.0;                  // np.unwrap along the horizon
     for (int k = 0; k < N; ++k) {
         const double th_raw = (k == 0) ? r0t : mpc_in_xref(a, i, k, 2);
@@ -274,6 +282,7 @@ B2C_HD int prep_instance(const MpcArgs& a, int64_t i, double* g, int64_t gst, do
 #pragma unroll
         for (int e = 0; e < MR; ++e) { const int c_ = mpc_class_of(d2min[e], hdr[6 + 3 * e]); cls = c_ < cls ? c_ : cls; }
     }
+    if (cls == MPC_MARGIN_CLASSES - 1 && fabs(hdr[2]) < 0.1) cls = MPC_NCLASS - 1;
     return cls;
 }
 
@@ -705,7 +714,11 @@ B2C_HD void slot_finish(const MpcArgs& a, const SlotMem& m, SlotState& s) {
     else           { a.u0[i] = u00; a.u0[B + i] = u01; }
     a.cost[i] = Jout;
     if (a.status) a.status[i] = s.st;
+#ifdef B2C_SLOT_TRACE
+    if (a.iters) a.iters[i] = s.it | (s.rounds << 8) | (s.round0 << 16);     // trace build only: packed for tools/slot_trace.py
+#else
     if (a.iters) a.iters[i] = s.it;
+#endif
     if (a.slack_used) a.slack_used[i] = (mv > 1e-6) ? 1 : 0;   // :485
     s.mode = SLOT_IDLE;
 }
@@ -869,16 +882,15 @@ k_mpc_slots(const MpcArgs a) {
     }
     SlotState s;
     s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0; s.rej = 0; s.undo = 0;
+    TRACE(s.rounds = 0; s.round0 = 0;)
     s.alpha = s.J = s.dec = s.z0x = s.z0y = s.z0t = s.lamx = s.lamy = s.lamt = s.max_viol = 0.0;
     bool empty = false;
     const int64_t nB = mpc_count(a);                          // instances in the queue (a.B stays the buffer stride)
-    unsigned long long cum0 = 0, cum1 = 0, cum2 = 0;          // class boundaries in queue order
-    if (a.perm) { cum0 = a.class_count[0]; cum1 = cum0 + a.class_count[1]; cum2 = cum1 + a.class_count[2]; }
     int64_t seen = 0;                                         // queue position at this warp's last claim
     TRACE(unsigned long long tr_t0 = trace_ns(); long long tr_b = 0, tr_r = 0, tr_f = 0, tr_c, tr_rounds = 0, tr_lanes = 0;
           long long tr_undo = 0, tr_team = 0, tr_sweep = 0, tr_post = 0, tr_teamrounds = 0, tr_c2 = 0, tr_tb = 0, tr_tf = 0, tr_bact = 0;)
     for (;;) {
-        TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE));)
+        TRACE(tr_c = clock64(); ++tr_rounds; tr_lanes += __popc(__ballot_sync(FULL, s.mode != SLOT_IDLE)); if (s.mode != SLOT_IDLE) ++s.rounds;)
         // ---- rejected trials are undone first (inputs from GW, gains from the mirror): the backward phase leaves the
         // strips of lanes without a sweep as they are, and with the mirror in tensor memory it rewrites every lane's
         // mirror from its strip, so strip and mirror must agree by then
@@ -922,8 +934,14 @@ k_mpc_slots(const MpcArgs a) {
                 if (id < nB) {
                     if (a.perm) {                             // queue position -> (class, offset) -> instance
                         const unsigned long long q = (unsigned long long)id;
-                        const int c = (q >= cum0) + (q >= cum1) + (q >= cum2);
-                        const unsigned long long lo = (c == 0) ? 0ull : (c == 1) ? cum0 : (c == 2) ? cum1 : cum2;
+                        int c = 0;
+                        unsigned long long lo = 0, hi = a.class_count[0];     // class boundaries in queue order
+#pragma unroll
+                        for (int e = 1; e < MPC_NCLASS; ++e) {
+                            const unsigned long long n = a.class_count[e];
+                            if (q >= hi) { c = e; lo = hi; }
+                            hi += n;
+                        }
                         id = (int64_t)a.perm[(int64_t)c * a.B + (int64_t)(q - lo)];
                     }
                     // the prepared record: header -> state + obstacle strip; the stage constants stay where they are
@@ -944,6 +962,7 @@ k_mpc_slots(const MpcArgs a) {
                     }
                     m.g = tile + (id & 31) * 6;
                     s.inst = id; s.it = 0; s.ls = 0; s.rej = 0; s.undo = 0; s.st = B2C_MAXITER;
+                    TRACE(s.rounds = 0; s.round0 = (int)tr_rounds;)
                     s.alpha = 0.0; s.dec = 0.0; s.max_viol = 0.0;
                     s.z0x = h0.x; s.z0y = h0.y; s.z0t = h1.x;
                     s.mode = SLOT_FWD_PLAIN;
@@ -1017,8 +1036,10 @@ k_mpc_slots(const MpcArgs a) {
                 t.it = __shfl_sync(FULL, s.it, src); t.st = __shfl_sync(FULL, s.st, src);
                 t.dec = __shfl_sync(FULL, s.dec, src);
                 t.z0x = __shfl_sync(FULL, s.z0x, src); t.z0y = __shfl_sync(FULL, s.z0y, src); t.z0t = __shfl_sync(FULL, s.z0t, src);
+                TRACE(t.rounds = __shfl_sync(FULL, s.rounds, src); t.round0 = __shfl_sync(FULL, s.round0, src);)
                 if (moved && lane == win) {                               // I take the instance over, trial accepted
                     s.inst = t.inst; s.it = t.it; s.st = t.st; s.dec = t.dec;
+                    TRACE(s.rounds = t.rounds; s.round0 = t.round0;)
                     s.z0x = t.z0x; s.z0y = t.z0y; s.z0t = t.z0t;
                     s.alpha = falpha; s.ls = ols + off; s.rej = 1; s.undo = 0;
                     s.J = Jn; s.max_viol = mv; s.lamx = lx; s.lamy = ly; s.lamt = lt;

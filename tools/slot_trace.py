@@ -50,7 +50,20 @@ def main():
     rounds = t[:, 2]
     cyc = t[:, 3:6]
     q = lambda a: [float(np.percentile(a, p)) for p in (0, 10, 50, 90, 100)]
+    raw = it.cpu().numpy().astype(np.int64)
+    it = torch.from_numpy(raw & 0xff)
+    res, r0 = (raw >> 8) & 0xff, (raw >> 16) & 0xffff          # rounds resident, warp round of the claim
+    itn = it.numpy()
+    extra = res - (itn + 1)                                     # rounds beyond one per iteration + the first evaluation
+    hard = np.argsort(-(r0 + res))[:12]
+    per_instance = {"rounds_resident_pct_50_90_99_100": [float(np.percentile(res, p)) for p in (50, 90, 99, 100)],
+                    "extra_rounds_mean": float(extra.mean()), "extra_rounds_max": int(extra.max()),
+                    "extra_rounds_hist": np.bincount(np.clip(extra, 0, 12)).tolist(),
+                    "last_finishers": [dict(claimed_in_round=int(r0[i]), rounds=int(res[i]), iters=int(itn[i])) for i in hard],
+                    "claim_round_of_iters_ge_10": sorted(r0[itn >= 10].tolist())[-10:],
+                    "rounds_of_iters_ge_10": sorted(res[itn >= 10].tolist())[-10:]}
     print(json.dumps({
+        "per_instance": per_instance,
         "B": B, "warps": len(t), "iters_mean": float(it.float().mean()), "iters_max": int(it.max()),
         "start_spread_us": float((t[:, 0].max() - t0) / 1e3),
         "warp_end_us_pct_0_10_50_90_100": q(end),
