@@ -35,6 +35,7 @@ struct MpcArgs {
     unsigned long long* queue;   // next unclaimed instance index
     int64_t nslots;              // resident slots (= grid * block)
     int mir;                     // slot kernel: the gains mirror is held in tensor memory (set by the launcher)
+    int fine_classes;            // slot kernel: six difficulty classes instead of four (set by the launcher)
     unsigned long long* class_count;   // instances per difficulty class (claim order), or unused
     uint32_t* perm;              // [class][B] instance ids in claim order; NULL = claim in index order
 };
@@ -99,7 +100,7 @@ static inline void mpc_fill_args(MpcArgs& a, int64_t B, const b2c_mpc_params* p,
     a.x0 = x0; a.xref = xref; a.uref = uref; a.obs = obs; a.step_count = step_count;
     a.u0 = u0; a.cost = cost; a.status = status; a.iters = iters; a.slack_used = slack_used;
     a.useq = useq; a.xpred = xpred;
-    a.scratch = nullptr; a.lam_off = 0; a.queue = nullptr; a.nslots = 0; a.mir = 0; a.class_count = nullptr; a.perm = nullptr;
+    a.scratch = nullptr; a.lam_off = 0; a.queue = nullptr; a.nslots = 0; a.mir = 0; a.fine_classes = 0; a.class_count = nullptr; a.perm = nullptr;
     a.in_aos = 0; a.out_aos = 0; a.table = nullptr; a.table_rows = 0; a.k0 = nullptr;
     a.rec = nullptr; a.rec_hdr = 0; a.rec_tile = 0;
 }

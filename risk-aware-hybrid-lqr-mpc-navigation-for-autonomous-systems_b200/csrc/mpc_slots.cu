@@ -283,6 +283,7 @@ B2C_HD int prep_instance(const MpcArgs& a, int64_t i, double* g, int64_t gst, do
         for (int e = 0; e < MR; ++e) { const int c_ = mpc_class_of(d2min[e], hdr[6 + 3 * e]); cls = c_ < cls ? c_ : cls; }
     }
     if (cls == MPC_MARGIN_CLASSES - 1 && fabs(hdr[2]) < 0.1) cls = MPC_NCLASS - 1;
+    if (!a.fine_classes && cls > 3) cls = 3;          // a batch that fills the slots many times over: the easy end as one class
     return cls;
 }
 
@@ -1176,6 +1177,8 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int) {
     // columns until the first exits): ask for more than half of the shared memory
     size_t smem = c.smem;
     // the gains mirror goes to tensor memory when U is in shared memory and N stages per warp fit the 512 columns
+    // the split of the easy end of the claim order matters when the last claims decide the makespan
+    a.fine_classes = (a.B <= (int64_t)5 * a.nslots) ? 1 : 0;
     a.mir = (c.kt == 0 && ((c.tpb + 127) / 128) * 16 * a.N <= 512) ? 1 : 0;
     if (const char* e = getenv("B2C_SLOTS_MIRROR")) a.mir = (a.mir && atoi(e) != 0) ? 1 : 0;   // developer switch (A/B runs)
     if ((c.kt > 0 || a.mir) && smem < 120 * 1024) smem = 120 * 1024;
