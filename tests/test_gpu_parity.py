@@ -617,8 +617,9 @@ def test_mpc_host_async_two_calls_in_flight(hc):
 @pytest.mark.parametrize("N,M,B", [(20, 5, 50000), (20, 5, 3000), (6, 3, 9000)])
 def test_mpc_slot_configurations_agree_bit_for_bit(hc, N, M, B, monkeypatch):
     """The slot kernel's configurations -- 256 slots per SM with the first 16 stages of the U strips in tensor memory
-    (tcgen05.ld / tcgen05.st), 128 slots per SM with everything in shared memory, 256 in shared memory for short
-    horizons -- run the same per-lane code on different storage: identical results, bit for bit."""
+    (tcgen05.ld / tcgen05.st), 128 slots per SM with the strips in shared memory and the gains mirror in tensor or
+    global memory, 256 in shared memory for short horizons -- run the same per-lane code on different storage:
+    identical results, bit for bit."""
     from hybrid_controller.controllers.mpc_controller import MPCController
     from hybrid_controller import workloads as wl
     x0, xr, ur, ob = wl.config4_instances(B, N=N, seed=N + M + B, obstacles=wl.DENSE_OBSTACLES[:M],
@@ -630,6 +631,12 @@ def test_mpc_slot_configurations_agree_bit_for_bit(hc, N, M, B, monkeypatch):
     for cfg in cfgs:
         monkeypatch.setenv("B2C_SLOTS_CFG", cfg)
         res[cfg] = mpc.solve_with_ltv_batch(x0, xr, ur, ob)
+    # the gains mirror of the shared-memory configurations: tensor memory (default) against global memory
+    monkeypatch.setenv("B2C_SLOTS_CFG", "128,0")
+    monkeypatch.setenv("B2C_SLOTS_MIRROR", "0")
+    res["128,0 / mirror in global memory"] = mpc.solve_with_ltv_batch(x0, xr, ur, ob)
+    cfgs.append("128,0 / mirror in global memory")
+    monkeypatch.delenv("B2C_SLOTS_MIRROR")
     monkeypatch.delenv("B2C_SLOTS_CFG")
     ref = res[cfgs[0]]
     assert (ref["status"] == 0).all() and ref["iters"].max() >= 5
