@@ -17,14 +17,19 @@
 //     256 KB of TMEM host 256 slots per SM at N = 20 -- two warps per scheduler -- where shared memory alone hosts 128.
 //     Neither sweep touches HBM for the sequential part of the recursion.
 //   * read-only per-stage constants (cos*dt, sin*dt, u_ref, p_ref) come from the instance's prepared record (L2)
-//     through a cp.async ring, two / three stages ahead; the gains are mirrored to a slot-indexed global strip
-//     GG[8N][nslots] and the inputs a trial replaces to GW[2N][nslots], so that a rejected line-search trial can be
-//     undone without re-running the Riccati sweep.
+//     through a cp.async ring, two / three stages ahead.
+//   * MIRRORS: the gains of the last backward sweep (GG[8N] per slot) and the inputs a trial replaces (GW[2N]) are
+//     kept a second time, so that a rejected line-search trial can be undone without re-running the Riccati sweep.
+//     When U is in shared memory, tensor memory is free and holds GG: one tcgen05.st.32x32b.x16 per stage for the 32
+//     lanes of a warp (a.mir; N stages of 16 columns per warp).  Otherwise GG is a slot-indexed global strip
+//     [8N][nslots]; GW always is ([2N][nslots]).  Four 16-byte global stores per lane and stage cost a warp that is
+//     alone on its scheduler a third of its backward sweep (they hold their source registers until the LSU has
+//     read them).
 //   * LANE REFILL: a lane whose instance has converged writes its outputs and immediately claims the next
 //     unsolved instance from a global queue (warp-aggregated atomicAdd); a refill is the record header (4 + 3M
-//     doubles).  Every round of the warp loop is  [backward | finish + refill | undo + forward].
-//   * every U access is warp-uniform (tcgen05.ld/st are .sync.aligned): all lanes of a warp run a sweep together,
-//     lanes without work compute on stale data and their side effects are switched off.
+//     doubles).  Every round of the warp loop is  [undo | backward | finish + refill | forward].
+//   * every U access is warp-uniform (tcgen05.ld/st are .sync.aligned): all lanes of a warp run a sweep together;
+//     lanes without work compute on stale data, their side effects are switched off and they put back what they read.
 //
 // The per-slot functions are B2C_HD so tests/ can run the identical state machine on the host
 // (-DB2C_HOST_EMUL, test-only library).
@@ -84,6 +89,23 @@ __device__ __forceinline__ void tm_st16(uint32_t taddr, const double (&u)[8]) {
 #pragma unroll
     for (int e = 0; e < 8; ++e) { r[2 * e] = (uint32_t)__double2loint(u[e]); r[2 * e + 1] = (uint32_t)__double2hiint(u[e]); }
     asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                    "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+// the same 16 columns written as eight register pairs: a double is a pair already, so no register has to be moved into
+// a block of 16 consecutive ones first (the x16 form costs 16 MOVs when the values come from different computations)
+__device__ __forceinline__ void tm_st2x8(uint32_t taddr, const double (&u)[8]) {
+    uint32_t r[16];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { r[2 * e] = (uint32_t)__double2loint(u[e]); r[2 * e + 1] = (uint32_t)__double2hiint(u[e]); }
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1,%2};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+2], {%3,%4};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+4], {%5,%6};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+6], {%7,%8};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+8], {%9,%10};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+10], {%11,%12};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+12], {%13,%14};\n\t"
+                 "tcgen05.st.sync.aligned.32x32b.x2.b32 [%0+14], {%15,%16};"
                  :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
                     "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
 }
@@ -466,7 +488,8 @@ B2C_HD double slot_forward(const MpcArgs& a, const SlotMem& m, const double z0x,
 // ----- backward sweep ------------------------------------------------------------------------------
 // Riccati recursion on the stored stage models with the block_size == 1 structure written out
 // (A = I + [0 0 al; 0 0 be; 0 0 0], B = [ck 0; sk 0; 0 dt], Hzz = [wxx wxy 0; wxy wyy 0; 0 0 q2], Huu = R).
-// Gains go to U (over the model they were computed from) and, for `act` lanes, are mirrored to GG.
+// Gains go to U (over the model they were computed from) and to the mirror GG: tensor memory (every lane stores; a
+// lane that is not `act` stores what it loaded, which is what its mirror holds) or the global strip (`act` lanes).
 template <int SS, int MT, int KT>
 B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState& s, const bool act) {
     const int N = a.N;
@@ -475,7 +498,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
     double v0 = s.lamx, v1 = s.lamy, v2 = s.lamt;     // value-function gradient
     double l0 = v0, l1 = v1, l2 = v2;                 // true costate
     double dec = 0.0;
-    // the mirror store of stage j+1 is issued one stage late, from registers nothing else wants in between
+    // global mirror: the store of stage j+1 is issued one stage late, from registers nothing else wants in between
     // (issued in place, the next writes to its source registers stalled on the store queue)
     double pm[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #if defined(__CUDA_ARCH__)
@@ -543,7 +566,7 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
         u[4] = act ? K11 : uold[4]; u[5] = act ? K12 : uold[5]; u[6] = act ? k0 : uold[6];  u[7] = act ? k1 : uold[7];
         u_store8<SS, KT>(m, j, u);
 #if defined(__CUDA_ARCH__)
-        if (mir) tm_st16(m.tmg + 16u * (uint32_t)j, u);   // the mirror: one warp-wide store (idempotent for the other lanes)
+        if (mir) tm_st2x8(m.tmg + 16u * (uint32_t)j, u);  // the mirror: warp-wide stores (idempotent for the other lanes)
 #endif
 #pragma unroll
         for (int e = 0; e < 8; ++e) pm[e] = u[e];
@@ -567,10 +590,10 @@ B2C_HD double slot_backward(const MpcArgs& a, const SlotMem& m, const SlotState&
 }
 
 // ----- undo a rejected trial -------------------------------------------------------------------------
-// Deferred to the start of the next forward phase and run by the whole warp (U accesses are warp-uniform): `pred`
-// lanes take their previous inputs back from GW and their gains from the mirror GG (what happened to their U strip
-// in between does not matter).  Other lanes keep their U.  Four stages of mirror loads are in flight together (one
-// L2 round trip per four stages instead of one per stage).
+// Deferred to the start of the next round and run by the whole warp (U accesses are warp-uniform): `pred` lanes take
+// their previous inputs back from GW and their gains from the mirror GG (what happened to their U strip in between
+// does not matter).  Other lanes keep their U.  Four stages of global loads are in flight together (one L2 round
+// trip per four stages instead of one per stage).
 template <int SS, int KT>
 B2C_HD void slot_undo(const MpcArgs& a, const SlotMem& m, const bool pred) {
     const int N = a.N;
