@@ -362,7 +362,7 @@ def test_mpc_ramp_fallback_and_edge_cases(hc):
         mpc.solve_with_ltv(xr2[0], xr2[:4], ur2[:3], [])
 
 
-@pytest.mark.parametrize("N,M,B", [(20, 5, 20000), (6, 3, 300), (10, 0, 77), (1, 2, 33), (40, 5, 5000), (85, 2, 700)])
+@pytest.mark.parametrize("N,M,B", [(20, 5, 20000), (6, 3, 300), (10, 0, 77), (1, 2, 33), (32, 3, 4000), (40, 5, 5000), (85, 2, 700)])
 def test_mpc_engines_agree(hc, N, M, B):
     """The slot kernel (shared-memory scratch, lane refill; 128 / 64 / 32 slots per CTA depending on N)
     and the general kernel run the same method: same iteration counts, results equal to rounding.
