@@ -804,6 +804,9 @@ k_mpc_prepare(const MpcArgs a) {
     __shared__ unsigned wcount[MPC_PREP_THREADS / 32][MPC_NCLASS];         // per warp, then exclusive prefix over warps
     __shared__ unsigned long long cbase[MPC_NCLASS];
     const int64_t i = (int64_t)blockIdx.x * MPC_PREP_THREADS + threadIdx.x, B = a.B;
+    // programmatic dependent launch: the slot kernel's CTAs may be scheduled while this grid is still running (they
+    // set up shared and tensor memory and then wait for this grid to complete, griddepcontrol.wait)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const bool valid = i < mpc_count(a);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int cls = -1;
@@ -904,6 +907,8 @@ k_mpc_slots(const MpcArgs a) {
         m.tmg = tmb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * (16 * a.N));
         if (KT == 0) __syncthreads();                         // everyone has the address before the ring is used
     }
+    // everything above is independent of the prepare pass; its records, class counts and claim order are read below
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     SlotState s;
     s.mode = SLOT_IDLE; s.inst = -1; s.it = 0; s.ls = 0; s.st = 0; s.rej = 0; s.undo = 0;
     TRACE(s.rounds = 0; s.round0 = 0;)
@@ -1178,7 +1183,14 @@ int64_t mpc_slots_scratch_bytes(const MpcArgs& a, int sm_count) {
 template <int SS, int MT, int KT>
 static int slots_launch_t(b2c_ctx* ctx, const MpcArgs& a, int grid, size_t smem) {
     B2C_CUDA(cudaFuncSetAttribute(k_mpc_slots<SS, MT, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SLOT_SMEM_CAP));
-    k_mpc_slots<SS, MT, KT><<<grid, SS, smem, ctx->stream>>>(a);
+    // launched as a programmatic dependent of k_mpc_prepare (the kernel before it in the stream)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)SS); cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    B2C_CUDA(cudaLaunchKernelEx(&cfg, k_mpc_slots<SS, MT, KT>, a));
     B2C_CHECK_LAUNCH(ctx);
     return 0;
 }
