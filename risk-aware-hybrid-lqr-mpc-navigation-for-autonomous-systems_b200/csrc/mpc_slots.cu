@@ -20,8 +20,8 @@
 //     through a cp.async ring, two / three stages ahead.
 //   * MIRRORS: the gains of the last backward sweep (GG[8N] per slot) and the inputs a trial replaces (GW[2N]) are
 //     kept a second time, so that a rejected line-search trial can be undone without re-running the Riccati sweep.
-//     When U is in shared memory, tensor memory is free and holds GG: one tcgen05.st.32x32b.x16 per stage for the 32
-//     lanes of a warp (a.mir; N stages of 16 columns per warp).  Otherwise GG is a slot-indexed global strip
+//     When U is in shared memory, tensor memory is free and holds GG: tcgen05.st.32x32b writes a stage for the 32
+//     lanes of a warp (a.mir; N stages of 16 columns per warp; eight .x2 stores, see tm_st2x8).  Otherwise GG is a slot-indexed global strip
 //     [8N][nslots]; GW always is ([2N][nslots]).  Four 16-byte global stores per lane and stage cost a warp that is
 //     alone on its scheduler a third of its backward sweep (they hold their source registers until the LSU has
 //     read them).
@@ -1211,9 +1211,9 @@ int mpc_slots_launch(b2c_ctx* ctx, MpcArgs& a, int) {
     // a kernel that allocates all of an SM's tensor memory must be alone on that SM (a second CTA would wait for
     // columns until the first exits): ask for more than half of the shared memory
     size_t smem = c.smem;
-    // the gains mirror goes to tensor memory when U is in shared memory and N stages per warp fit the 512 columns
     // the split of the easy end of the claim order matters when the last claims decide the makespan
     a.fine_classes = (a.B <= (int64_t)5 * a.nslots) ? 1 : 0;
+    // the gains mirror goes to tensor memory when U is in shared memory and N stages per warp fit the 512 columns
     a.mir = (c.kt == 0 && ((c.tpb + 127) / 128) * 16 * a.N <= 512) ? 1 : 0;
     if (const char* e = getenv("B2C_SLOTS_MIRROR")) a.mir = (a.mir && atoi(e) != 0) ? 1 : 0;   // developer switch (A/B runs)
     if ((c.kt > 0 || a.mir) && smem < 120 * 1024) smem = 120 * 1024;
